@@ -1,0 +1,155 @@
+/* include/rgs_capi.h -- C ABI of librgs_b200.so, the B200 (sm_100a) batched GameSim physics core.
+ *
+ * This is the drop-in boundary for ONE path of goromal/robo-game-sim: the GameSim step
+ * (reference include/GameSim.h:16-27, src/GameSim.cpp:21-623) that the reference exposes to
+ * Python through pybind11 (reference src/RoboGamePy.cpp:11-25).  Plain pointers and sizes only;
+ * no torch / pybind / Eigen types cross this boundary.  Every function returns 0 on success or a
+ * negative RGS_E* code; rgs_last_error() gives a thread-local message.  No exception crosses.
+ *
+ * Pointer naming: d_* = CUDA device pointer on the batch's device, h_* = host pointer.
+ * All device work is enqueued on `stream` (a cudaStream_t passed as void*; NULL = the legacy
+ * default stream) and is asynchronous unless stated otherwise.
+ *
+ * Layouts (game-major records: a warp owns a game, so lanes read consecutive words of ONE record):
+ *   state  record  [2 + 4E] doubles, reference order [TAS, TBS, PK(px,py,vx,vy), A1.., B1..]
+ *                  (reference include/SimState.h:14-23), E = 2*players_per_team + 1
+ *   action record  [2n][2] commanded velocities in team order A1..An, B1..Bn
+ *                  (the four Vector2d arguments of GameSim::run, reference src/GameSim.cpp:118-119)
+ *   events record  int64[RGS_N_EVENTS], see enum below
+ *   traj   record  [1 + (2+4E) + (2n)^2] doubles = [t, state, damage(aggressor,victim) row-major]
+ */
+#ifndef RGS_CAPI_H
+#define RGS_CAPI_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RGS_GRID_POINTS 50 /* COLLISION_GRID_POINTS, reference include/GameSim.h:6 */
+#define RGS_COUNTER_LIM 50 /* COLLISION_COUNTER_LIM, reference include/GameSim.h:7 */
+#define RGS_MAX_TEAM 7
+#define RGS_N_EVENTS 16
+#define RGS_N_STATS 64
+
+enum { RGS_OK = 0, RGS_EINVAL = -1, RGS_ECUDA = -2, RGS_ENOMEM = -3, RGS_EUNSUPPORTED = -4 };
+
+/* precision / formulation of a batch */
+enum {
+    RGS_MODE_EXACT_F64 = 64, /* K1: reference operator order, fp64, no FMA: event-exact parity mode */
+    RGS_MODE_FAST_F32 = 32,  /* K2: exact affine sub-step map, fp32, FMA: throughput mode */
+    RGS_MODE_FAST_F64 = 65   /* K2 instantiated in fp64 (validation of the K2 formulation) */
+};
+
+/* events record fields (identical to the oracle's, oracle/gamesim_oracle.h) */
+enum {
+    RGS_EV_GOALS_A = 0, RGS_EV_GOALS_B = 1,
+    RGS_EV_WALL_UP = 2, RGS_EV_WALL_DOWN = 3, RGS_EV_WALL_RIGHT = 4, RGS_EV_WALL_LEFT = 5,
+    RGS_EV_PLAYER_PLAYER = 6, RGS_EV_PLAYER_PUCK = 7,
+    RGS_EV_DISCARDED = 8, RGS_EV_LOOP_ITERS = 9, RGS_EV_LIVE_STEPS = 10, RGS_EV_DECIDED_STEP = 11,
+    RGS_EV_COUNTER_LIMIT = 12, RGS_EV_BASE_CLAMP = 13, RGS_EV_HASH = 14, RGS_EV_OVERLAP_FIXES = 15
+};
+
+/* stats vector fields, int64[RGS_N_STATS] (K4; summed over games, all-reduced over GPUs by the caller) */
+enum {
+    RGS_ST_GAMES = 0, RGS_ST_WINS_A = 1, RGS_ST_WINS_B = 2, RGS_ST_UNDECIDED = 3,
+    RGS_ST_LEAD_A = 4, RGS_ST_LEAD_B = 5, RGS_ST_TIED = 6, /* by score at the end, decided or not */
+    RGS_ST_EVENTS0 = 8,      /* + RGS_EV_*: sums of the first 14 event fields (not the hash) */
+    RGS_ST_SCORE_HIST = 32,  /* + 5*min(TAS,4) + min(TBS,4): 25-bin joint score histogram */
+};
+
+/* Constructor constants (reference src/GameSim.cpp:5-9) and reset() arguments (:21-25). */
+typedef struct rgs_params {
+    double dt;                /* 0.05 */
+    int32_t winning_score;    /* reset() argument */
+    int32_t players_per_team; /* 2 = reference; up to RGS_MAX_TEAM */
+    double noise;             /* process-noise stdev; must be 0 in RGS_MODE_EXACT_F64 */
+    double tau_puck, tau_player, player_mass, puck_mass;
+    double arena_x, arena_y, player_radius, puck_radius, goal_height; /* 10, 5, 0.2, 0.175, 1.0 */
+    int32_t mode;             /* RGS_MODE_* */
+    int32_t reserved;
+} rgs_params;
+
+typedef struct rgs_batch rgs_batch; /* opaque: N independent games resident on one GPU */
+
+/* Reference defaults: GameSim::GameSim() + the default arguments of GameSim::reset. */
+void rgs_default_params(rgs_params *p);
+
+const char *rgs_last_error(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+int64_t rgs_launch_count(void);
+int rgs_device_count(int *out);
+
+/* replaces: GameSim::GameSim() (reference src/GameSim.cpp:3-17) for n_games games at once. */
+int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_params *p);
+int rgs_batch_destroy(rgs_batch *b);
+int rgs_batch_set_params(rgs_batch *b, const rgs_params *p); /* n_games, team size and mode are fixed */
+
+/* replaces: GameSim::reset (reference src/GameSim.cpp:21-55) -- K5.
+ *   d_x0_ball [n_games,4] doubles (x0_stride doubles between games; 0 = one puck state shared by
+ *             all games) or NULL -> zeros; players start at x=-+X/4, y_k = Y/2-(k+1/2)Y/n.
+ *   d_state0  [n_games, 2+4E] doubles or NULL; when given it overrides the whole state
+ *             (checkpoint restore; the reference has no equivalent).
+ * Clock, damage and event records are zeroed. */
+int rgs_batch_reset(rgs_batch *b, const double *d_x0_ball, int64_t x0_stride, const double *d_state0, void *stream);
+
+/* replaces: n_steps consecutive calls of GameSim::run (reference src/GameSim.cpp:118-171) on every
+ * game -- K1 / K2, ONE fused launch, state resident on chip across all n_steps.
+ *   d_actions  action records of the batch's compute type (double for *_F64 modes, float for
+ *              RGS_MODE_FAST_F32): game g, step k reads record
+ *              d_actions + g*act_game_stride + min(k / hold, n_act-1) * 4n     (strides in elements;
+ *              act_game_stride 0 = one action sequence shared by all games)
+ *   d_traj     NULL, or [n_games, n_steps/log_stride] traj records: the state after every
+ *              log_stride-th step (steps log_stride-1, 2*log_stride-1, ...)
+ * Games whose score reached winning_score are frozen, as GameSim::run is (:121-123). */
+int rgs_batch_run(rgs_batch *b, const void *d_actions, int64_t n_act, int64_t hold, int64_t act_game_stride,
+                  int64_t n_steps, int64_t log_stride, double *d_traj, void *stream);
+
+/* Same, with the synthetic S0 action generator evaluated on chip (no action tensor in HBM):
+ * player commands ~ U(-u_max,u_max)^2 redrawn every `hold` steps from Philox4x32-10 keyed by
+ * (seed, first_game + g, step0/hold + k/hold); identical to rgs_synth_actions' output. */
+int rgs_batch_run_synth(rgs_batch *b, uint64_t seed, int64_t first_game, int64_t step0, int64_t hold, double u_max,
+                        int64_t n_steps, int64_t log_stride, double *d_traj, void *stream);
+
+/* State / clock / damage / events of all games into caller-provided DEVICE buffers (any may be NULL). */
+int rgs_batch_get(rgs_batch *b, double *d_state, double *d_t, double *d_damage, int64_t *d_events, void *stream);
+
+/* K4: reduce scores + event records of the whole batch into int64[RGS_N_STATS] on the device
+ * (overwritten).  Multi-GPU callers sum these vectors with one NCCL all-reduce. */
+int rgs_batch_stats(rgs_batch *b, int64_t *d_stats, void *stream);
+
+/* K5 (synthetic inputs "S0", shared by bench, tests and the CPU baseline):
+ *   d_x0_ball [n,4] doubles: px~U(-4,4), py~U(-2,2), vx,vy~U(-3,3)
+ *   d_actions [n, n_act, 2*players_per_team, 2] of `dtype` (32 = float, 64 = double) ~ U(-u_max,u_max)
+ * keyed by (seed, first_game + g, action index); either pointer may be NULL. */
+int rgs_synth_inputs(int device, uint64_t seed, int64_t first_game, int64_t n, int32_t players_per_team,
+                     int64_t n_act, double u_max, double *d_x0_ball, void *d_actions, int32_t dtype, void *stream);
+
+/* Host-buffer entry point (the call MonteCarlo-style callers make; bench.py's e2e): copies
+ * h_x0_ball [n_games,4] doubles and h_actions [n_games,n_act,4n] (compute type) to the device in
+ * chunks overlapped with compute, runs n_steps, and returns final states [n_games,2+4E] doubles,
+ * events [n_games,RGS_N_EVENTS] and stats int64[RGS_N_STATS] into host buffers (any of the three
+ * may be NULL).  Synchronous: returns when the outputs are valid. */
+int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_actions, int64_t n_act, int64_t hold,
+                       int64_t n_steps, double *h_state, int64_t *h_events, int64_t *h_stats);
+
+/* Batch-of-one convenience used by the drop-in class robo_game_py.GameSim
+ * (replaces reference src/RoboGamePy.cpp:15-24 one to one). */
+typedef struct rgs_single rgs_single;
+int rgs_single_create(rgs_single **out, int device);
+int rgs_single_destroy(rgs_single *s);
+/* GameSim::reset: h_x0_ball[4]; logname NULL or "" with log=0; h_out_state22 receives the state. */
+int rgs_single_reset(rgs_single *s, double dt, int32_t winning_score, const double *h_x0_ball, double noise,
+                     int32_t log, const char *logname, int32_t seed, double tau_puck, double tau_player,
+                     double player_mass, double puck_mass, double *h_out_state22);
+int rgs_single_undecided(rgs_single *s, int32_t *out);
+/* GameSim::run: h_actions8 = [A1x,A1y,A2x,A2y,B1x,B1y,B2x,B2y]. */
+int rgs_single_run(rgs_single *s, const double *h_actions8, double *h_out_state22);
+int rgs_single_time(rgs_single *s, double *out_t);
+int rgs_single_damage(rgs_single *s, double *h_out16);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RGS_CAPI_H */
