@@ -26,6 +26,9 @@
 #ifdef __cplusplus
 extern "C" {
 #endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)
+#endif
 
 #define RGS_GRID_POINTS 50 /* COLLISION_GRID_POINTS, reference include/GameSim.h:6 */
 #define RGS_COUNTER_LIM 50 /* COLLISION_COUNTER_LIM, reference include/GameSim.h:7 */
@@ -126,6 +129,10 @@ int rgs_batch_stats(rgs_batch *b, int64_t *d_stats, void *stream);
 int rgs_synth_inputs(int device, uint64_t seed, int64_t first_game, int64_t n, int32_t players_per_team,
                      int64_t n_act, double u_max, double *d_x0_ball, void *d_actions, int32_t dtype, void *stream);
 
+/* Roofline denominator measured on the spot: dependent-FMA-chain micro-kernel on every SM, fp32
+ * (fp64 = 0) or fp64 (fp64 = 1); result in FMA TFLOP/s (2 flop per FMA).  Synchronous. */
+int rgs_measure_peak(int device, int32_t fp64, double *out_tflops);
+
 /* Host-buffer entry point (the call MonteCarlo-style callers make; bench.py's e2e): copies
  * h_x0_ball [n_games,4] doubles and h_actions [n_games,n_act,4n] (compute type) to the device in
  * chunks overlapped with compute, runs n_steps, and returns final states [n_games,2+4E] doubles,
@@ -149,6 +156,9 @@ int rgs_single_run(rgs_single *s, const double *h_actions8, double *h_out_state2
 int rgs_single_time(rgs_single *s, double *out_t);
 int rgs_single_damage(rgs_single *s, double *h_out16);
 
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,559 @@
+// rgs_capi.cu -- the C ABI of librgs_b200.so (declared in include/rgs_capi.h).
+//
+// Host-side runtime of the batched GameSim path: owns the device-resident game records
+// (state / clock / damage / events, game-major), validates arguments, launches the sm_100a kernels
+// (K1 exact fp64, K2 fast fp32/fp64, K4 statistics, K5 reset + synthetic inputs) and implements
+// the batch-of-one handle behind the drop-in Python class robo_game_py.GameSim
+// (reference src/RoboGamePy.cpp:11-25).  No exception crosses this boundary and there is NO CPU
+// implementation of the step anywhere in this library: without a CUDA device every entry point
+// that would compute returns RGS_ECUDA.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "rgs_host_params.h"
+#include "rgs_kernels.h"
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<int64_t> g_launches{0};
+
+int fail(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+    return fail(RGS_ECUDA, "%s: %s (%s)", what, cudaGetErrorString(e), cudaGetErrorName(e));
+}
+
+#define RGS_CUDA(call)                                         \
+    do {                                                       \
+        cudaError_t e__ = (call);                              \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call);  \
+    } while (0)
+
+
+int check_params(const rgs_params *p) {
+    if (!p) return fail(RGS_EINVAL, "params is NULL");
+    if (p->players_per_team < 1 || p->players_per_team > RGS_MAX_TEAM)
+        return fail(RGS_EINVAL, "players_per_team must be 1..%d (got %d)", RGS_MAX_TEAM, p->players_per_team);
+    if (p->mode != RGS_MODE_EXACT_F64 && p->mode != RGS_MODE_FAST_F32 && p->mode != RGS_MODE_FAST_F64)
+        return fail(RGS_EINVAL, "mode must be RGS_MODE_EXACT_F64, RGS_MODE_FAST_F32 or RGS_MODE_FAST_F64 (got %d)", p->mode);
+    if (!(p->dt > 0.0)) return fail(RGS_EINVAL, "dt must be > 0");
+    if (!(p->tau_puck > 0.0) || !(p->tau_player > 0.0)) return fail(RGS_EINVAL, "tau_puck and tau_player must be > 0");
+    if (!(p->player_mass > 0.0) || !(p->puck_mass > 0.0)) return fail(RGS_EINVAL, "masses must be > 0");
+    if (!(p->arena_x > 0.0) || !(p->arena_y > 0.0) || !(p->player_radius > 0.0) || !(p->puck_radius > 0.0))
+        return fail(RGS_EINVAL, "arena and radii must be > 0");
+    if (p->noise != 0.0)
+        return fail(RGS_EUNSUPPORTED,
+                    "process noise is not implemented: every shipped reference script runs noise=0 and the "
+                    "reference's libstdc++ normal_distribution stream is not reproducible bit for bit");
+    return RGS_OK;
+}
+
+}  // namespace
+
+struct rgs_batch {
+    int device = 0;
+    int sm_count = 148;
+    int64_t n_games = 0;
+    rgs_params p{};
+    int n_team = 2, E = 5, srec = 22, dmg_rec = 16;
+    double *state = nullptr, *clock = nullptr, *damage = nullptr;
+    long long *events = nullptr, *stats = nullptr;
+    // staging for rgs_batch_run_host
+    void *stage_actions = nullptr;
+    size_t stage_actions_bytes = 0;
+    double *stage_x0 = nullptr;
+    cudaStream_t streams[2] = {nullptr, nullptr};
+    cudaEvent_t done_ev[2] = {nullptr, nullptr};
+};
+
+namespace {
+
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) { ok = false; return; }
+        if (prev != dev && cudaSetDevice(dev) != cudaSuccess) ok = false;
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+// one fused launch over games [g0, g1) of the batch
+int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64_t n_act, int64_t hold,
+              int64_t act_game_stride, int64_t n_steps, int64_t log_stride, double *d_traj, int synth, uint64_t seed,
+              int64_t first_game, int64_t step0, double u_max, cudaStream_t stream) {
+    if (g1 <= g0 || n_steps == 0) return RGS_OK;
+    rgs::RunArgs A{};
+    const int np = 2 * b->n_team;
+    A.n_games = g1 - g0;
+    A.state = b->state + g0 * b->srec;
+    A.clock = b->clock + g0;
+    A.damage = b->damage + g0 * b->dmg_rec;
+    A.events = b->events + g0 * RGS_N_EVENTS;
+    const size_t esz = b->p.mode == RGS_MODE_FAST_F32 ? sizeof(float) : sizeof(double);
+    A.actions = d_actions ? static_cast<const char *>(d_actions) + (size_t)(g0 * act_game_stride) * esz : nullptr;
+    A.n_act = n_act;
+    A.hold = hold;
+    A.act_game_stride = act_game_stride;
+    A.n_steps = n_steps;
+    A.log_stride = log_stride;
+    A.traj = d_traj ? d_traj + g0 * (n_steps / (log_stride > 0 ? log_stride : 1)) * (1 + b->srec + np * np) : nullptr;
+    A.synth = synth;
+    A.seed = seed;
+    A.first_game = first_game + g0;
+    A.step0 = step0;
+    A.u_max = u_max;
+    cudaError_t e;
+    switch (b->p.mode) {
+    case RGS_MODE_EXACT_F64:
+        e = rgs::launch_rollout_exact(b->n_team, rgs::make_dev_params<double>(b->p), A, stream, b->sm_count);
+        break;
+    case RGS_MODE_FAST_F32:
+        e = rgs::launch_rollout_fast_f32(b->n_team, b->p, A, stream, b->sm_count);
+        break;
+    default:
+        e = rgs::launch_rollout_fast_f64(b->n_team, b->p, A, stream, b->sm_count);
+        break;
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "rollout kernel launch");
+    g_launches.fetch_add(1);
+    return RGS_OK;
+}
+
+int check_run_args(rgs_batch *b, int64_t n_act, int64_t hold, int64_t n_steps, int64_t log_stride, const double *d_traj) {
+    if (!b) return fail(RGS_EINVAL, "batch is NULL");
+    if (n_steps < 0) return fail(RGS_EINVAL, "n_steps must be >= 0");
+    if (hold < 1) return fail(RGS_EINVAL, "hold must be >= 1");
+    if (n_act < 1) return fail(RGS_EINVAL, "n_act must be >= 1");
+    if (log_stride < 0) return fail(RGS_EINVAL, "log_stride must be >= 0");
+    if (d_traj && log_stride == 0) return fail(RGS_EINVAL, "d_traj given but log_stride is 0");
+    return RGS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+void rgs_default_params(rgs_params *p) {
+    if (!p) return;
+    std::memset(p, 0, sizeof(*p));
+    p->dt = 0.05;
+    p->winning_score = 3;
+    p->players_per_team = 2;
+    p->noise = 0.0;
+    p->tau_puck = 0.1;
+    p->tau_player = 0.5;
+    p->player_mass = 1.0;
+    p->puck_mass = 0.5;
+    p->arena_x = 10.0;
+    p->arena_y = 5.0;
+    p->player_radius = 0.2;
+    p->puck_radius = 0.175;
+    p->goal_height = 1.0;
+    p->mode = RGS_MODE_EXACT_F64;
+}
+
+const char *rgs_last_error(void) { return g_err; }
+int64_t rgs_launch_count(void) { return g_launches.load(); }
+
+int rgs_device_count(int *out) {
+    if (!out) return fail(RGS_EINVAL, "out is NULL");
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        *out = 0;
+        return cuda_fail(e, "cudaGetDeviceCount");
+    }
+    *out = n;
+    return RGS_OK;
+}
+
+int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_params *p) {
+    if (!out) return fail(RGS_EINVAL, "out is NULL");
+    *out = nullptr;
+    if (n_games < 0) return fail(RGS_EINVAL, "n_games must be >= 0");
+    int rc = check_params(p);
+    if (rc != RGS_OK) return rc;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(RGS_ECUDA, "no CUDA device available (%s); this library has no CPU path",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= ndev) return fail(RGS_EINVAL, "device %d out of range (0..%d)", device, ndev - 1);
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(RGS_ECUDA, "cudaSetDevice(%d) failed", device);
+    rgs_batch *b = new (std::nothrow) rgs_batch();
+    if (!b) return fail(RGS_ENOMEM, "out of host memory");
+    b->device = device;
+    b->n_games = n_games;
+    b->p = *p;
+    b->n_team = p->players_per_team;
+    b->E = 2 * b->n_team + 1;
+    b->srec = 2 + 4 * b->E;
+    b->dmg_rec = 4 * b->n_team * b->n_team;
+    cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
+    const size_t n = (size_t)(n_games > 0 ? n_games : 1);
+    cudaError_t err = cudaSuccess;
+    if (err == cudaSuccess) err = cudaMalloc(&b->state, n * b->srec * sizeof(double));
+    if (err == cudaSuccess) err = cudaMalloc(&b->clock, n * sizeof(double));
+    if (err == cudaSuccess) err = cudaMalloc(&b->damage, n * b->dmg_rec * sizeof(double));
+    if (err == cudaSuccess) err = cudaMalloc(&b->events, n * RGS_N_EVENTS * sizeof(long long));
+    if (err == cudaSuccess) err = cudaMalloc(&b->stats, RGS_N_STATS * sizeof(long long));
+    if (err != cudaSuccess) {
+        rgs_batch_destroy(b);
+        cudaGetLastError();
+        return fail(err == cudaErrorMemoryAllocation ? RGS_ENOMEM : RGS_ECUDA, "device allocation for %lld games failed: %s",
+                    (long long)n_games, cudaGetErrorString(err));
+    }
+    *out = b;
+    int rc2 = rgs_batch_reset(b, nullptr, 0, nullptr, nullptr);
+    if (rc2 != RGS_OK) {
+        rgs_batch_destroy(b);
+        *out = nullptr;
+        return rc2;
+    }
+    return RGS_OK;
+}
+
+int rgs_batch_destroy(rgs_batch *b) {
+    if (!b) return RGS_OK;
+    DeviceGuard guard(b->device);
+    cudaDeviceSynchronize();
+    cudaFree(b->state);
+    cudaFree(b->clock);
+    cudaFree(b->damage);
+    cudaFree(b->events);
+    cudaFree(b->stats);
+    cudaFree(b->stage_actions);
+    cudaFree(b->stage_x0);
+    for (int k = 0; k < 2; ++k) {
+        if (b->streams[k]) cudaStreamDestroy(b->streams[k]);
+        if (b->done_ev[k]) cudaEventDestroy(b->done_ev[k]);
+    }
+    delete b;
+    return RGS_OK;
+}
+
+int rgs_batch_set_params(rgs_batch *b, const rgs_params *p) {
+    if (!b) return fail(RGS_EINVAL, "batch is NULL");
+    int rc = check_params(p);
+    if (rc != RGS_OK) return rc;
+    if (p->players_per_team != b->n_team) return fail(RGS_EINVAL, "players_per_team is fixed at create time");
+    if (p->mode != b->p.mode) return fail(RGS_EINVAL, "mode is fixed at create time");
+    b->p = *p;
+    return RGS_OK;
+}
+
+int rgs_batch_reset(rgs_batch *b, const double *d_x0_ball, int64_t x0_stride, const double *d_state0, void *stream) {
+    if (!b) return fail(RGS_EINVAL, "batch is NULL");
+    if (x0_stride != 0 && x0_stride < 4) return fail(RGS_EINVAL, "x0_stride must be 0 (shared) or >= 4");
+    if (b->n_games == 0) return RGS_OK;
+    DeviceGuard guard(b->device);
+    cudaError_t e = rgs::launch_reset(b->n_team, b->n_games, b->p, d_x0_ball, x0_stride, d_state0, b->state, b->clock,
+                                      b->damage, b->events, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "reset kernel launch");
+    g_launches.fetch_add(1);
+    return RGS_OK;
+}
+
+int rgs_batch_run(rgs_batch *b, const void *d_actions, int64_t n_act, int64_t hold, int64_t act_game_stride,
+                  int64_t n_steps, int64_t log_stride, double *d_traj, void *stream) {
+    int rc = check_run_args(b, n_act, hold, n_steps, log_stride, d_traj);
+    if (rc != RGS_OK) return rc;
+    if (!d_actions) return fail(RGS_EINVAL, "d_actions is NULL");
+    if (act_game_stride < 0) return fail(RGS_EINVAL, "act_game_stride must be >= 0");
+    DeviceGuard guard(b->device);
+    return run_range(b, 0, b->n_games, d_actions, n_act, hold, act_game_stride, n_steps, log_stride, d_traj, 0, 0, 0, 0, 0.0,
+                     static_cast<cudaStream_t>(stream));
+}
+
+int rgs_batch_run_synth(rgs_batch *b, uint64_t seed, int64_t first_game, int64_t step0, int64_t hold, double u_max,
+                        int64_t n_steps, int64_t log_stride, double *d_traj, void *stream) {
+    int rc = check_run_args(b, 1, hold, n_steps, log_stride, d_traj);
+    if (rc != RGS_OK) return rc;
+    if (step0 < 0) return fail(RGS_EINVAL, "step0 must be >= 0");
+    DeviceGuard guard(b->device);
+    return run_range(b, 0, b->n_games, nullptr, 1, hold, 0, n_steps, log_stride, d_traj, 1, seed, first_game, step0, u_max,
+                     static_cast<cudaStream_t>(stream));
+}
+
+int rgs_batch_get(rgs_batch *b, double *d_state, double *d_t, double *d_damage, int64_t *d_events, void *stream) {
+    if (!b) return fail(RGS_EINVAL, "batch is NULL");
+    if (b->n_games == 0) return RGS_OK;
+    DeviceGuard guard(b->device);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const size_t n = (size_t)b->n_games;
+    // cudaMemcpyDefault: the destination may be device memory or (pinned / pageable) host memory
+    if (d_state) RGS_CUDA(cudaMemcpyAsync(d_state, b->state, n * b->srec * sizeof(double), cudaMemcpyDefault, s));
+    if (d_t) RGS_CUDA(cudaMemcpyAsync(d_t, b->clock, n * sizeof(double), cudaMemcpyDefault, s));
+    if (d_damage) RGS_CUDA(cudaMemcpyAsync(d_damage, b->damage, n * b->dmg_rec * sizeof(double), cudaMemcpyDefault, s));
+    if (d_events) RGS_CUDA(cudaMemcpyAsync(d_events, b->events, n * RGS_N_EVENTS * sizeof(long long), cudaMemcpyDefault, s));
+    return RGS_OK;
+}
+
+int rgs_batch_stats(rgs_batch *b, int64_t *d_stats, void *stream) {
+    if (!b) return fail(RGS_EINVAL, "batch is NULL");
+    if (!d_stats) return fail(RGS_EINVAL, "d_stats is NULL");
+    DeviceGuard guard(b->device);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    cudaError_t e = rgs::launch_stats(b->n_team, b->n_games, b->state, b->events, b->p.winning_score, b->stats, s, b->sm_count);
+    if (e != cudaSuccess) return cuda_fail(e, "stats kernel launch");
+    g_launches.fetch_add(1);
+    RGS_CUDA(cudaMemcpyAsync(d_stats, b->stats, RGS_N_STATS * sizeof(long long), cudaMemcpyDefault, s));
+    return RGS_OK;
+}
+
+int rgs_synth_inputs(int device, uint64_t seed, int64_t first_game, int64_t n, int32_t players_per_team, int64_t n_act,
+                     double u_max, double *d_x0_ball, void *d_actions, int32_t dtype, void *stream) {
+    if (n < 0 || n_act < 0) return fail(RGS_EINVAL, "n and n_act must be >= 0");
+    if (players_per_team < 1 || players_per_team > RGS_MAX_TEAM) return fail(RGS_EINVAL, "players_per_team out of range");
+    if (dtype != 32 && dtype != 64) return fail(RGS_EINVAL, "dtype must be 32 or 64");
+    if (n == 0 || (!d_x0_ball && (!d_actions || n_act == 0))) return RGS_OK;
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(RGS_ECUDA, "cudaSetDevice(%d) failed", device);
+    cudaError_t e = rgs::launch_synth(seed, first_game, n, players_per_team, n_act, u_max, d_x0_ball,
+                                      n_act > 0 ? d_actions : nullptr, dtype, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "synth kernel launch");
+    g_launches.fetch_add(1);
+    return RGS_OK;
+}
+
+int rgs_measure_peak(int device, int32_t fp64, double *out_tflops) {
+    if (!out_tflops) return fail(RGS_EINVAL, "out_tflops is NULL");
+    DeviceGuard guard(device);
+    if (!guard.ok) return fail(RGS_ECUDA, "cudaSetDevice(%d) failed", device);
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    cudaError_t e = rgs::measure_fma_peak(fp64 ? 1 : 0, sms, out_tflops);
+    if (e != cudaSuccess) return cuda_fail(e, "fma peak micro-kernel");
+    g_launches.fetch_add(6);
+    return RGS_OK;
+}
+
+int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_actions, int64_t n_act, int64_t hold,
+                       int64_t n_steps, double *h_state, int64_t *h_events, int64_t *h_stats) {
+    int rc = check_run_args(b, n_act, hold, n_steps, 0, nullptr);
+    if (rc != RGS_OK) return rc;
+    if (!h_actions) return fail(RGS_EINVAL, "h_actions is NULL");
+    DeviceGuard guard(b->device);
+    const int64_t N = b->n_games;
+    const size_t esz = b->p.mode == RGS_MODE_FAST_F32 ? sizeof(float) : sizeof(double);
+    const int64_t arec = n_act * 4 * b->n_team;  // action elements per game
+    const size_t need = (size_t)N * arec * esz;
+    if (b->stage_actions_bytes < need) {
+        cudaFree(b->stage_actions);
+        b->stage_actions = nullptr;
+        b->stage_actions_bytes = 0;
+        cudaError_t e = cudaMalloc(&b->stage_actions, need ? need : 1);
+        if (e != cudaSuccess) return fail(RGS_ENOMEM, "staging %zu action bytes: %s", need, cudaGetErrorString(e));
+        b->stage_actions_bytes = need;
+    }
+    if (h_x0_ball && !b->stage_x0) RGS_CUDA(cudaMalloc(&b->stage_x0, (size_t)(N > 0 ? N : 1) * 4 * sizeof(double)));
+    for (int k = 0; k < 2; ++k) {
+        if (!b->streams[k]) RGS_CUDA(cudaStreamCreateWithFlags(&b->streams[k], cudaStreamNonBlocking));
+        if (!b->done_ev[k]) RGS_CUDA(cudaEventCreateWithFlags(&b->done_ev[k], cudaEventDisableTiming));
+    }
+    // Game-range chunks, double-buffered over two streams: the H2D copy of chunk c+1 and the D2H
+    // copy of chunk c-1 overlap the rollout of chunk c (games are independent, so a chunk is
+    // simply a contiguous slice of the batch).
+    int64_t n_chunks = N >= 65536 ? 8 : 1;
+    const int64_t per = (N + n_chunks - 1) / (n_chunks > 0 ? n_chunks : 1);
+    for (int64_t c = 0; c < n_chunks; ++c) {
+        const int64_t g0 = c * per, g1 = (g0 + per < N) ? g0 + per : N;
+        if (g1 <= g0) break;
+        cudaStream_t s = b->streams[c & 1];
+        const int64_t ng = g1 - g0;
+        RGS_CUDA(cudaMemcpyAsync(static_cast<char *>(b->stage_actions) + (size_t)g0 * arec * esz,
+                                 static_cast<const char *>(h_actions) + (size_t)g0 * arec * esz, (size_t)ng * arec * esz,
+                                 cudaMemcpyHostToDevice, s));
+        if (h_x0_ball)
+            RGS_CUDA(cudaMemcpyAsync(b->stage_x0 + g0 * 4, h_x0_ball + g0 * 4, (size_t)ng * 4 * sizeof(double),
+                                     cudaMemcpyHostToDevice, s));
+        cudaError_t e = rgs::launch_reset(b->n_team, ng, b->p, h_x0_ball ? b->stage_x0 + g0 * 4 : nullptr, 4, nullptr,
+                                          b->state + g0 * b->srec, b->clock + g0, b->damage + g0 * b->dmg_rec,
+                                          b->events + g0 * RGS_N_EVENTS, s);
+        if (e != cudaSuccess) return cuda_fail(e, "reset kernel launch");
+        g_launches.fetch_add(1);
+        rc = run_range(b, g0, g1, b->stage_actions, n_act, hold, arec, n_steps, 0, nullptr, 0, 0, 0, 0, 0.0, s);
+        if (rc != RGS_OK) return rc;
+        if (h_state)
+            RGS_CUDA(cudaMemcpyAsync(h_state + g0 * b->srec, b->state + g0 * b->srec, (size_t)ng * b->srec * sizeof(double),
+                                     cudaMemcpyDeviceToHost, s));
+        if (h_events)
+            RGS_CUDA(cudaMemcpyAsync(h_events + g0 * RGS_N_EVENTS, b->events + g0 * RGS_N_EVENTS,
+                                     (size_t)ng * RGS_N_EVENTS * sizeof(long long), cudaMemcpyDeviceToHost, s));
+        RGS_CUDA(cudaEventRecord(b->done_ev[c & 1], s));
+    }
+    // statistics over the whole batch once both streams have drained into stream 0
+    RGS_CUDA(cudaStreamWaitEvent(b->streams[0], b->done_ev[1], 0));
+    if (h_stats) {
+        rc = rgs_batch_stats(b, h_stats, b->streams[0]);
+        if (rc != RGS_OK) return rc;
+    }
+    RGS_CUDA(cudaStreamSynchronize(b->streams[1]));
+    RGS_CUDA(cudaStreamSynchronize(b->streams[0]));
+    return RGS_OK;
+}
+
+}  // extern "C"
+
+// ---- batch-of-one handle behind robo_game_py.GameSim -----------------------------------------
+struct rgs_single {
+    int device = 0;
+    rgs_batch *b = nullptr;
+    rgs_params p{};
+    double *d_act = nullptr, *d_x0 = nullptr;
+    double *h_pin = nullptr;  // pinned scratch: [0..21] state, [22..29] actions, [30] clock, [32..47] damage
+    cudaStream_t stream = nullptr;
+    FILE *log = nullptr;
+    bool is_reset = false;
+    double h_state[22];
+};
+
+extern "C" {
+
+int rgs_single_create(rgs_single **out, int device) {
+    if (!out) return fail(RGS_EINVAL, "out is NULL");
+    *out = nullptr;
+    rgs_single *s = new (std::nothrow) rgs_single();
+    if (!s) return fail(RGS_ENOMEM, "out of host memory");
+    s->device = device;
+    rgs_default_params(&s->p);
+    int rc = rgs_batch_create(&s->b, device, 1, &s->p);
+    if (rc != RGS_OK) { delete s; return rc; }
+    DeviceGuard guard(device);
+    cudaError_t e = cudaMalloc(&s->d_act, 8 * sizeof(double));
+    if (e == cudaSuccess) e = cudaMalloc(&s->d_x0, 4 * sizeof(double));
+    if (e == cudaSuccess) e = cudaMallocHost(&s->h_pin, 64 * sizeof(double));
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+    if (e != cudaSuccess) { rgs_single_destroy(s); return cuda_fail(e, "rgs_single_create"); }
+    *out = s;
+    return RGS_OK;
+}
+
+int rgs_single_destroy(rgs_single *s) {
+    if (!s) return RGS_OK;
+    {
+        DeviceGuard guard(s->device);
+        if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
+        cudaFree(s->d_act);
+        cudaFree(s->d_x0);
+        if (s->h_pin) cudaFreeHost(s->h_pin);
+    }
+    if (s->log) fclose(s->log);
+    rgs_batch_destroy(s->b);
+    delete s;
+    return RGS_OK;
+}
+
+int rgs_single_reset(rgs_single *s, double dt, int32_t winning_score, const double *h_x0_ball, double noise, int32_t log,
+                     const char *logname, int32_t seed, double tau_puck, double tau_player, double player_mass,
+                     double puck_mass, double *h_out_state22) {
+    (void)seed;  // the seed only feeds the process-noise stream, which is identically scaled by noise = 0
+    if (!s) return fail(RGS_EINVAL, "handle is NULL");
+    if (!h_x0_ball) return fail(RGS_EINVAL, "x0_ball is NULL");
+    rgs_params p = s->p;
+    p.dt = dt;
+    p.winning_score = winning_score;
+    p.noise = noise;
+    p.tau_puck = tau_puck;
+    p.tau_player = tau_player;
+    p.player_mass = player_mass;
+    p.puck_mass = puck_mass;
+    int rc = rgs_batch_set_params(s->b, &p);
+    if (rc != RGS_OK) return rc;
+    s->p = p;
+    DeviceGuard guard(s->device);
+    std::memcpy(s->h_pin + 22, h_x0_ball, 4 * sizeof(double));
+    RGS_CUDA(cudaMemcpyAsync(s->d_x0, s->h_pin + 22, 4 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+    rc = rgs_batch_reset(s->b, s->d_x0, 4, nullptr, s->stream);
+    if (rc != RGS_OK) return rc;
+    RGS_CUDA(cudaMemcpyAsync(s->h_pin, s->b->state, 22 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+    RGS_CUDA(cudaStreamSynchronize(s->stream));
+    std::memcpy(s->h_state, s->h_pin, sizeof(s->h_state));
+    if (h_out_state22) std::memcpy(h_out_state22, s->h_state, sizeof(s->h_state));
+    // Logger::open (reference include/utils.h:54-59): close, then reopen truncating; a failed open is silent
+    if (s->log) { fclose(s->log); s->log = nullptr; }
+    if (log && logname && logname[0]) s->log = fopen(logname, "wb");
+    s->is_reset = true;
+    return RGS_OK;
+}
+
+int rgs_single_undecided(rgs_single *s, int32_t *out) {
+    if (!s || !out) return fail(RGS_EINVAL, "NULL argument");
+    if (!s->is_reset) return fail(RGS_EINVAL, "reset() has not been called");
+    *out = (s->h_state[0] < (double)s->p.winning_score) && (s->h_state[1] < (double)s->p.winning_score);
+    return RGS_OK;
+}
+
+int rgs_single_run(rgs_single *s, const double *h_actions8, double *h_out_state22) {
+    if (!s || !h_actions8) return fail(RGS_EINVAL, "NULL argument");
+    if (!s->is_reset) return fail(RGS_EINVAL, "reset() has not been called");
+    int32_t live = 0;
+    rgs_single_undecided(s, &live);
+    if (live) {  // GameSim::run is a no-op once decided (reference src/GameSim.cpp:121-123)
+        DeviceGuard guard(s->device);
+        std::memcpy(s->h_pin + 22, h_actions8, 8 * sizeof(double));
+        RGS_CUDA(cudaMemcpyAsync(s->d_act, s->h_pin + 22, 8 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
+        int rc = rgs_batch_run(s->b, s->d_act, 1, 1, 0, 1, 0, nullptr, s->stream);
+        if (rc != RGS_OK) return rc;
+        RGS_CUDA(cudaMemcpyAsync(s->h_pin, s->b->state, 22 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+        if (s->log) {
+            RGS_CUDA(cudaMemcpyAsync(s->h_pin + 30, s->b->clock, sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+            RGS_CUDA(cudaMemcpyAsync(s->h_pin + 32, s->b->damage, 16 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
+        }
+        RGS_CUDA(cudaStreamSynchronize(s->stream));
+        std::memcpy(s->h_state, s->h_pin, sizeof(s->h_state));
+        if (s->log) {
+            // 29-double record (reference src/GameSim.cpp:161-170).  damage.row(k) is written by
+            // include/utils.h:75 as 4 CONTIGUOUS doubles from &damage(k,0) of a column-major 4x4,
+            // i.e. column-major linear indices k..k+3; reproduced so files are byte-identical.
+            double rec[29];
+            const double *st = s->h_state, *dm = s->h_pin + 32;  // dm: (aggressor, victim) row-major
+            rec[0] = s->h_pin[30];
+            rec[1] = st[0]; rec[2] = st[1];
+            rec[3] = st[2]; rec[4] = st[3];
+            rec[5] = st[6]; rec[6] = st[7];
+            rec[7] = st[10]; rec[8] = st[11];
+            rec[9] = st[14]; rec[10] = st[15];
+            rec[11] = st[18]; rec[12] = st[19];
+            for (int k = 0; k < 4; ++k)
+                for (int c = 0; c < 4; ++c) {
+                    const int lin = k + c, row = lin % 4, col = lin / 4;
+                    rec[13 + 4 * k + c] = dm[row * 4 + col];
+                }
+            fwrite(rec, sizeof(double), 29, s->log);
+            fflush(s->log);
+        }
+    }
+    if (h_out_state22) std::memcpy(h_out_state22, s->h_state, sizeof(s->h_state));
+    return RGS_OK;
+}
+
+int rgs_single_time(rgs_single *s, double *out_t) {
+    if (!s || !out_t) return fail(RGS_EINVAL, "NULL argument");
+    DeviceGuard guard(s->device);
+    RGS_CUDA(cudaMemcpy(out_t, s->b->clock, sizeof(double), cudaMemcpyDeviceToHost));
+    return RGS_OK;
+}
+
+int rgs_single_damage(rgs_single *s, double *h_out16) {
+    if (!s || !h_out16) return fail(RGS_EINVAL, "NULL argument");
+    DeviceGuard guard(s->device);
+    RGS_CUDA(cudaMemcpy(h_out16, s->b->damage, 16 * sizeof(double), cudaMemcpyDeviceToHost));
+    return RGS_OK;
+}
+
+}  // extern "C"

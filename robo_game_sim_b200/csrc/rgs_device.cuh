@@ -6,9 +6,21 @@
 // lanes -> consecutive words, conflict free) and the first overlapping column of an owner is
 // found with one __ballot_sync.  The event queue (<= one event per owner body, reference
 // src/GameSim.cpp:136-150) is a tiny per-warp table read by broadcast.
+//
+// The kernel BODIES in rgs_*.cuh are plain C++ over a small set of warp intrinsics
+// (__shfl_sync, __ballot_sync, __syncwarp) so that tests/emu can compile the very same source with
+// g++ and step a warp on the CPU (fiber-per-lane emulator; test infrastructure only, the product
+// has no CPU path).  RGS_HOST_EMU is defined only by tests/emu/warp_emu.h.
 #pragma once
 #include <cstdint>
+#ifndef RGS_HOST_EMU
 #include <cuda_runtime.h>
+#define RGS_DEV __device__ __forceinline__
+#endif
+
+#ifndef RGS_TRACE
+#define RGS_TRACE(...) ((void)0)   // tests/emu may define it to print the event sequence
+#endif
 
 #include "../../include/rgs_capi.h"
 
@@ -85,7 +97,7 @@ __host__ __device__ inline double sym_uniform(uint32_t bits, double a) {
 }
 
 // Component `comp` (0 .. 4n-1) of the synthetic action record `aidx` of global game `game`.
-__device__ inline double synth_action(uint64_t seed, int64_t game, int64_t aidx, int comp, double u_max) {
+RGS_DEV double synth_action(uint64_t seed, int64_t game, int64_t aidx, int comp, double u_max) {
     uint32_t o[4];
     philox4x32_10((uint32_t)game, (uint32_t)((uint64_t)game >> 32), (uint32_t)aidx,
                   ((uint32_t)((uint64_t)aidx >> 32) << 8) | (uint32_t)(comp >> 2), (uint32_t)seed,
@@ -98,22 +110,19 @@ template <typename T, int NT>
 struct WarpSlice {
     static constexpr int E = 2 * NT + 1;
     T grid[4 * E * kGS];
+    T cmd[32];       // commanded velocity of body e, axis a at [2e+a] (fast kernel: run-time indexed reads)
     T qt[16];        // queued event time per owner body
     int qinfo[16];   // (seq << 8) | (kind << 4) | (j & 15), j = 15 for walls
     long long ev[RGS_N_EVENTS];
 };
 
 template <typename T>
-__device__ __forceinline__ T &G(T *grid, int e, int c, int col) { return grid[(e * 4 + c) * kGS + col]; }
+RGS_DEV T &G(T *grid, int e, int c, int col) { return grid[(e * 4 + c) * kGS + col]; }
 
 template <typename T>
-__device__ __forceinline__ T shfl(T v, int src);
-template <>
-__device__ __forceinline__ double shfl<double>(double v, int src) { return __shfl_sync(kFull, v, src); }
-template <>
-__device__ __forceinline__ float shfl<float>(float v, int src) { return __shfl_sync(kFull, v, src); }
+RGS_DEV T shfl(T v, int src) { return __shfl_sync(kFull, v, src); }
 
-__device__ __forceinline__ void hash_event(long long *ev, long long live, int kind, int i, int j, int goal) {
+RGS_DEV void hash_event(long long *ev, long long live, int kind, int i, int j, int goal) {
     unsigned long long h = (unsigned long long)ev[RGS_EV_HASH];
     const unsigned long long w = ((unsigned long long)live << 16) | ((unsigned long long)kind << 12) |
                                  ((unsigned long long)i << 8) | ((unsigned long long)(j < 0 ? 15 : j) << 4) |
@@ -129,7 +138,7 @@ __device__ __forceinline__ void hash_event(long long *ev, long long live, int ki
 // first column whose candidate falls inside this step, its lane broadcasts the event.
 // t0 is the simulator clock t_ (0 in step-relative mode).  Uniform return value.
 template <typename T, int NT>
-__device__ __forceinline__ bool scan_owner(T *grid, const DevParams<T> &P, int id, int base, T t0, int lane, T &out_t,
+RGS_DEV bool scan_owner(T *grid, const DevParams<T> &P, int id, int base, T t0, int lane, T &out_t,
                                            int &out_j, int &out_kind) {
     constexpr int E = 2 * NT + 1, PK = 2 * NT;
     const int ty = (id == PK);
@@ -210,7 +219,7 @@ __device__ __forceinline__ bool scan_owner(T *grid, const DevParams<T> &P, int i
 // Collision.h:24-30); the element executed next is the LAST one: smallest t, and among equal
 // times the most recently inserted.
 template <typename T, int NT>
-__device__ __forceinline__ void queue_push(WarpSlice<T, NT> *W, unsigned &qmask, int &seq, int owner, T t, int j, int kind,
+RGS_DEV void queue_push(WarpSlice<T, NT> *W, unsigned &qmask, int &seq, int owner, T t, int j, int kind,
                                            int lane) {
     if (lane == 0) {
         W->qt[owner] = t;
@@ -222,7 +231,7 @@ __device__ __forceinline__ void queue_push(WarpSlice<T, NT> *W, unsigned &qmask,
 }
 
 template <typename T, int NT>
-__device__ __forceinline__ void queue_pop(WarpSlice<T, NT> *W, unsigned &qmask, int &ei, int &ej, int &ekind, T &et) {
+RGS_DEV void queue_pop(WarpSlice<T, NT> *W, unsigned &qmask, int &ei, int &ej, int &ekind, T &et) {
     constexpr int E = 2 * NT + 1;
     int best = -1, binfo = 0;
     T bt = T(0);
@@ -244,7 +253,7 @@ __device__ __forceinline__ void queue_pop(WarpSlice<T, NT> *W, unsigned &qmask, 
 
 // Drop queued events sharing a body with the executed one (GameSim.cpp:347-352).
 template <typename T, int NT>
-__device__ __forceinline__ void queue_prune(WarpSlice<T, NT> *W, unsigned &qmask, int ei, int ej) {
+RGS_DEV void queue_prune(WarpSlice<T, NT> *W, unsigned &qmask, int ei, int ej) {
     constexpr int E = 2 * NT + 1;
 #pragma unroll
     for (int e = 0; e < E; ++e) {

@@ -1,0 +1,33 @@
+// rgs_kernels.h -- launchers of the sm_100a kernels (one translation unit per kernel family so the
+// exact kernel can be built with -fmad=false while the throughput kernel keeps FMA contraction).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "rgs_device.cuh"
+
+namespace rgs {
+
+// K1: fp64, reference operator order (rgs_exact_kernel.cu)
+cudaError_t launch_rollout_exact(int n_team, const DevParams<double> &P, const RunArgs &A, cudaStream_t stream,
+                                 int sm_count);
+
+// K2: exact affine sub-step map, step-relative time, FMA; fp32 (throughput) and fp64 (validation
+// of the formulation against the oracle) instantiations (rgs_fast_kernel.cu)
+cudaError_t launch_rollout_fast_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
+cudaError_t launch_rollout_fast_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
+
+// K4: per-batch statistics vector int64[RGS_N_STATS] (rgs_aux_kernels.cu)
+cudaError_t launch_stats(int n_team, int64_t n_games, const double *state, const long long *events, int winning_score,
+                         long long *d_stats, cudaStream_t stream, int sm_count);
+
+// K5: batched reset + synthetic S0 inputs (rgs_aux_kernels.cu)
+cudaError_t launch_reset(int n_team, int64_t n_games, const rgs_params &p, const double *d_x0_ball, int64_t x0_stride,
+                         const double *d_state0, double *state, double *clock, double *damage, long long *events,
+                         cudaStream_t stream);
+cudaError_t launch_synth(uint64_t seed, int64_t first_game, int64_t n, int n_team, int64_t n_act, double u_max,
+                         double *d_x0_ball, void *d_actions, int dtype, cudaStream_t stream);
+
+// FMA-chain micro-benchmark: the measured FP32 / FP64 issue peak used as the roofline denominator
+cudaError_t measure_fma_peak(int fp64, int sm_count, double *tflops);
+
+}  // namespace rgs

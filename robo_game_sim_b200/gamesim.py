@@ -1,0 +1,317 @@
+"""Host-side mirror of the reference's Python surface for the GameSim path.
+
+`GameSim` is a drop-in for the pybind11 class `robo_game_py.GameSim`
+(reference src/RoboGamePy.cpp:11-25): same method names, argument order, return types
+(fresh float64[22] arrays) and `__repr__`; the five trailing `reset` arguments take the C++ default
+values (reference src/GameSim.cpp:24-25) that four of the reference's own scripts rely on
+(py/run_sim.py:43, py/test_collisions.py:26, ...).  Every call goes through the C ABI
+(include/rgs_capi.h) into the sm_100a kernels; a batch of one game is latency-bound by design and
+exists for API compatibility.
+
+`BatchedGameSim` is the new entry point: N independent games resident on one B200, advanced S steps
+per fused launch from device-resident action tensors (torch is used for tensor hand-off only).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _capi
+
+_MODES = {"exact": _capi.MODE_EXACT_F64, "fast": _capi.MODE_FAST_F32, "fast64": _capi.MODE_FAST_F64,
+          _capi.MODE_EXACT_F64: _capi.MODE_EXACT_F64, _capi.MODE_FAST_F32: _capi.MODE_FAST_F32,
+          _capi.MODE_FAST_F64: _capi.MODE_FAST_F64}
+
+
+def _vec(x, n, name):
+    """pybind11/eigen.h accepts any float-convertible 1-D length-n (or (n,1)) array."""
+    try:
+        a = np.asarray(x, dtype=np.float64)
+    except (TypeError, ValueError) as exc:
+        raise TypeError(f"{name}: expected {n} floats") from exc
+    if a.shape not in ((n,), (n, 1), (1, n)):
+        raise TypeError(f"{name}: expected an array of shape ({n},), got {a.shape}")
+    return np.ascontiguousarray(a.reshape(n))
+
+
+class GameSim:
+    """Drop-in for robo_game_py.GameSim (one 2v2 game, fp64 event-exact kernel K1)."""
+
+    def __init__(self, device=0):
+        self._lib = _capi.load()
+        self._h = C.c_void_p()
+        _capi.check(self._lib.rgs_single_create(C.byref(self._h), int(device)))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            self._lib.rgs_single_destroy(h)
+            self._h = None
+
+    def reset(self, dt, winning_score, x0_ball, noise, log, logname, seed=0, tau_puck=0.1, tau_player=0.5,
+              player_mass=1.0, puck_mass=0.5):
+        """GameSim::reset (reference src/GameSim.cpp:21-55) -> float64[22]."""
+        x0 = _vec(x0_ball, 4, "x0_ball")
+        if not isinstance(logname, (str, bytes)):
+            raise TypeError("logname: expected str")
+        name = logname.encode() if isinstance(logname, str) else logname
+        out = np.empty(22, dtype=np.float64)
+        _capi.check(self._lib.rgs_single_reset(
+            self._h, float(dt), int(winning_score), x0.ctypes.data_as(C.POINTER(C.c_double)), float(noise),
+            1 if log else 0, name, int(seed), float(tau_puck), float(tau_player), float(player_mass), float(puck_mass),
+            out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
+    def undecided(self):
+        """GameSim::undecided (reference src/GameSim.cpp:57-60)."""
+        flag = C.c_int32(0)
+        _capi.check(self._lib.rgs_single_undecided(self._h, C.byref(flag)))
+        return bool(flag.value)
+
+    def run(self, vel_A1, vel_A2, vel_B1, vel_B2):
+        """GameSim::run (reference src/GameSim.cpp:118-124): one game-step -> float64[22] copy."""
+        act = np.concatenate([_vec(vel_A1, 2, "vel_A1"), _vec(vel_A2, 2, "vel_A2"), _vec(vel_B1, 2, "vel_B1"),
+                              _vec(vel_B2, 2, "vel_B2")])
+        out = np.empty(22, dtype=np.float64)
+        _capi.check(self._lib.rgs_single_run(self._h, act.ctypes.data_as(C.POINTER(C.c_double)),
+                                             out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
+    # --- not in the reference binding (its clock and damage only reach the log file) ---
+    def time(self):
+        t = C.c_double(0.0)
+        _capi.check(self._lib.rgs_single_time(self._h, C.byref(t)))
+        return t.value
+
+    def damage(self):
+        out = np.empty(16, dtype=np.float64)
+        _capi.check(self._lib.rgs_single_damage(self._h, out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out.reshape(4, 4)
+
+    def __repr__(self):
+        return "GameSim Object"  # reference src/RoboGamePy.cpp:20-23
+
+
+class BatchedGameSim:
+    """N independent games on one GPU behind the C ABI (rgs_batch_*).
+
+    mode: "exact" (K1, fp64, event-exact vs. the reference), "fast" (K2, fp32 throughput),
+    "fast64" (K2 in fp64).  Keyword parameters are those of GameSim::reset plus the constructor
+    constants (arena_x, arena_y, player_radius, puck_radius, goal_height)."""
+
+    def __init__(self, n_games, device=None, mode="exact", players_per_team=2, **params):
+        import torch  # tensor hand-off only
+
+        self._torch = torch
+        self._lib = _capi.load()
+        if device is None:
+            device = torch.cuda.current_device() if torch.cuda.is_available() else 0
+        self.device = torch.device("cuda", int(device)) if not isinstance(device, torch.device) else device
+        self.n_games = int(n_games)
+        self.n_team = int(players_per_team)
+        self.n_bodies = 2 * self.n_team + 1
+        self.state_size = 2 + 4 * self.n_bodies
+        p = _capi.default_params()
+        if mode not in _MODES:
+            raise ValueError(f"mode must be one of 'exact', 'fast', 'fast64' (got {mode!r})")
+        p.mode = _MODES[mode]
+        p.players_per_team = self.n_team
+        for k, v in params.items():
+            if not hasattr(p, k) or k in ("mode", "players_per_team", "reserved"):
+                raise TypeError(f"unknown parameter {k!r}")
+            setattr(p, k, v)
+        self.params = p
+        self.mode = p.mode
+        self.action_dtype = torch.float32 if p.mode == _capi.MODE_FAST_F32 else torch.float64
+        self._h = C.c_void_p()
+        _capi.check(self._lib.rgs_batch_create(C.byref(self._h), self.device.index or 0, self.n_games, C.byref(p)))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            self._lib.rgs_batch_destroy(h)
+            self._h = None
+
+    # ---- helpers ----
+    def _stream(self):
+        return C.c_void_p(self._torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _dev_tensor(self, t, dtype, name):
+        torch = self._torch
+        if not isinstance(t, torch.Tensor):
+            t = torch.as_tensor(np.asarray(t), dtype=dtype)
+        if t.device != self.device:
+            t = t.to(self.device, non_blocking=True)
+        if t.dtype != dtype:
+            t = t.to(dtype)
+        return t.contiguous()
+
+    def set_params(self, **params):
+        for k, v in params.items():
+            if not hasattr(self.params, k) or k in ("mode", "players_per_team", "reserved"):
+                raise TypeError(f"unknown parameter {k!r}")
+            setattr(self.params, k, v)
+        _capi.check(self._lib.rgs_batch_set_params(self._h, C.byref(self.params)))
+
+    # ---- GameSim::reset for the whole batch ----
+    def reset(self, x0_ball=None, state0=None):
+        """x0_ball: None (zeros), [4] (shared) or [N,4]; state0: [N, 2+4E] full-state restore."""
+        torch = self._torch
+        x0_ptr, stride, keep = None, 0, []
+        if x0_ball is not None:
+            x0 = self._dev_tensor(x0_ball, torch.float64, "x0_ball")
+            if x0.numel() == 4:
+                stride = 0
+            elif tuple(x0.shape) == (self.n_games, 4):
+                stride = 4
+            else:
+                raise ValueError(f"x0_ball must have shape (4,) or ({self.n_games}, 4), got {tuple(x0.shape)}")
+            x0_ptr = x0.data_ptr()
+            keep.append(x0)
+        s0_ptr = None
+        if state0 is not None:
+            s0 = self._dev_tensor(state0, torch.float64, "state0")
+            if tuple(s0.shape) != (self.n_games, self.state_size):
+                raise ValueError(f"state0 must have shape ({self.n_games}, {self.state_size})")
+            s0_ptr = s0.data_ptr()
+            keep.append(s0)
+        _capi.check(self._lib.rgs_batch_reset(self._h, x0_ptr, stride, s0_ptr, self._stream()))
+        self._keep = keep  # borrowed until the stream op completes
+        return self
+
+    # ---- n_steps x GameSim::run for the whole batch, one fused launch ----
+    def run(self, actions, n_steps=None, hold=1, log_stride=0):
+        """actions: [N, n_act, 2n, 2] per-game or [n_act, 2n, 2] shared; step k uses action
+        min(k // hold, n_act-1).  Returns the trajectory tensor [N, n_steps//log_stride, 1+S+(2n)^2]
+        when log_stride > 0, else None."""
+        torch = self._torch
+        a = self._dev_tensor(actions, self.action_dtype, "actions")
+        np2 = 2 * self.n_team
+        if a.dim() == 4 and tuple(a.shape[0:1] + a.shape[2:]) == (self.n_games, np2, 2):
+            n_act, stride = a.shape[1], a.shape[1] * np2 * 2
+        elif a.dim() == 3 and tuple(a.shape[1:]) == (np2, 2):
+            n_act, stride = a.shape[0], 0
+        else:
+            raise ValueError(f"actions must have shape ({self.n_games}, n_act, {np2}, 2) or (n_act, {np2}, 2), "
+                             f"got {tuple(a.shape)}")
+        if n_steps is None:
+            n_steps = n_act * hold
+        traj, traj_ptr = None, None
+        if log_stride:
+            traj = torch.empty((self.n_games, n_steps // log_stride, 1 + self.state_size + np2 * np2),
+                               dtype=torch.float64, device=self.device)
+            traj_ptr = traj.data_ptr()
+        _capi.check(self._lib.rgs_batch_run(self._h, a.data_ptr(), n_act, int(hold), stride, int(n_steps),
+                                            int(log_stride), traj_ptr, self._stream()))
+        self._keep = [a]
+        return traj
+
+    def run_synth(self, seed, n_steps, hold=10, u_max=10.0, first_game=0, step0=0, log_stride=0):
+        """Same, with the synthetic S0 commands generated on chip (no action tensor in HBM)."""
+        torch = self._torch
+        traj, traj_ptr = None, None
+        if log_stride:
+            np2 = 2 * self.n_team
+            traj = torch.empty((self.n_games, n_steps // log_stride, 1 + self.state_size + np2 * np2),
+                               dtype=torch.float64, device=self.device)
+            traj_ptr = traj.data_ptr()
+        _capi.check(self._lib.rgs_batch_run_synth(self._h, int(seed), int(first_game), int(step0), int(hold),
+                                                  float(u_max), int(n_steps), int(log_stride), traj_ptr, self._stream()))
+        return traj
+
+    # ---- read-back (device tensors) ----
+    def _get(self, which):
+        torch = self._torch
+        np2 = 2 * self.n_team
+        shapes = {"state": ((self.n_games, self.state_size), torch.float64), "time": ((self.n_games,), torch.float64),
+                  "damage": ((self.n_games, np2, np2), torch.float64), "events": ((self.n_games, _capi.N_EVENTS), torch.int64)}
+        shape, dt = shapes[which]
+        out = torch.empty(shape, dtype=dt, device=self.device)
+        ptrs = {k: (out.data_ptr() if k == which else None) for k in shapes}
+        _capi.check(self._lib.rgs_batch_get(self._h, ptrs["state"], ptrs["time"], ptrs["damage"], ptrs["events"],
+                                            self._stream()))
+        return out
+
+    def state(self):
+        return self._get("state")
+
+    def time(self):
+        return self._get("time")
+
+    def damage(self):
+        return self._get("damage")
+
+    def events(self):
+        return self._get("events")
+
+    def undecided(self):
+        s = self.state()
+        w = float(self.params.winning_score)
+        return (s[:, 0] < w) & (s[:, 1] < w)
+
+    def stats(self):
+        """K4: int64[64] statistics vector on the device (sum it across GPUs with one all-reduce)."""
+        torch = self._torch
+        out = torch.empty(_capi.N_STATS, dtype=torch.int64, device=self.device)
+        _capi.check(self._lib.rgs_batch_stats(self._h, out.data_ptr(), self._stream()))
+        return out
+
+    # ---- host-buffer entry point (end-to-end path) ----
+    def run_host(self, x0_ball, actions, n_steps, hold=1, want_state=True, want_events=True, out=None):
+        """x0_ball [N,4] float64 and actions [N,n_act,2n,2] (float32 in "fast" mode, else float64)
+        in HOST memory (numpy or CPU torch tensors, ideally pinned).  Resets the batch, runs n_steps
+        and returns (state [N,S] f64, events [N,16] i64, stats [64] i64) as numpy arrays."""
+        torch = self._torch
+
+        def host(x, dtype):
+            if isinstance(x, torch.Tensor):
+                if x.is_cuda:
+                    raise ValueError("run_host takes host buffers; use run() for device tensors")
+                x = x.numpy()
+            return np.ascontiguousarray(x, dtype=dtype)
+
+        adt = np.float32 if self.mode == _capi.MODE_FAST_F32 else np.float64
+        a = host(actions, adt)
+        np2 = 2 * self.n_team
+        if a.ndim != 4 or (a.shape[0], a.shape[2], a.shape[3]) != (self.n_games, np2, 2):
+            raise ValueError(f"actions must have shape ({self.n_games}, n_act, {np2}, 2), got {a.shape}")
+        x0 = None
+        if x0_ball is not None:
+            x0 = host(x0_ball, np.float64)
+            if x0.shape != (self.n_games, 4):
+                raise ValueError(f"x0_ball must have shape ({self.n_games}, 4)")
+        out = out or {}
+        st = out.get("state") if want_state else None
+        ev = out.get("events") if want_events else None
+        if want_state and st is None:
+            st = np.empty((self.n_games, self.state_size), dtype=np.float64)
+        if want_events and ev is None:
+            ev = np.empty((self.n_games, _capi.N_EVENTS), dtype=np.int64)
+        stats = np.zeros(_capi.N_STATS, dtype=np.int64)
+
+        def ptr(x):
+            if x is None:
+                return None
+            return x.data_ptr() if isinstance(x, torch.Tensor) else x.ctypes.data
+
+        _capi.check(self._lib.rgs_batch_run_host(self._h, ptr(x0), ptr(a), a.shape[1], int(hold), int(n_steps), ptr(st),
+                                                 ptr(ev), stats.ctypes.data))
+        return st, ev, stats
+
+
+def synth_inputs(n, n_act, seed=0, first_game=0, players_per_team=2, u_max=10.0, dtype=None, device=None,
+                 want_x0=True, want_actions=True):
+    """K5: the synthetic S0 inputs (x0_ball [n,4] f64, actions [n,n_act,2n,2]) generated on the device."""
+    import torch
+
+    lib = _capi.load()
+    if device is None:
+        device = torch.cuda.current_device()
+    dev = torch.device("cuda", int(device)) if not isinstance(device, torch.device) else device
+    dtype = dtype or torch.float64
+    x0 = torch.empty((n, 4), dtype=torch.float64, device=dev) if want_x0 else None
+    acts = torch.empty((n, n_act, 2 * players_per_team, 2), dtype=dtype, device=dev) if want_actions else None
+    _capi.check(lib.rgs_synth_inputs(dev.index or 0, int(seed), int(first_game), int(n), int(players_per_team),
+                                     int(n_act), float(u_max), x0.data_ptr() if want_x0 else None,
+                                     acts.data_ptr() if want_actions else None, 32 if dtype == torch.float32 else 64,
+                                     C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)))
+    return x0, acts

@@ -1,0 +1,24 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+@pytest.fixture(scope="session")
+def golden():
+    import numpy as np
+
+    return np.load(os.path.join(ROOT, "tests", "golden", "gamesim_golden.npz"))
+
+
+GOLDEN_CASES = ["kat1_goal", "kat2_wall_up", "kat3_player_wall", "kat4_head_on", "bounce_kick_up", "bounce_kick_down",
+                "wall_contacts", "decided_freeze"]

@@ -1,0 +1,95 @@
+// tests/emu/emu_rollout.cpp -- TEST INFRASTRUCTURE ONLY (never on the product path).
+//
+// Compiles the product's kernel-body headers (robo_game_sim_b200/csrc/rgs_exact.cuh, rgs_fast.cuh)
+// with g++ against the fiber warp emulator (warp_emu.h) so their control flow and arithmetic can be
+// checked against the oracle in this GPU-less container.  The resulting tests/emu/librgs_emu.so is
+// loaded by tests/ only; robo_game_sim_b200 never loads it and has no CPU path.
+#include "warp_emu.h"
+//
+#include "../../robo_game_sim_b200/csrc/rgs_exact.cuh"
+#include "../../robo_game_sim_b200/csrc/rgs_fast.cuh"
+#include "../../robo_game_sim_b200/csrc/rgs_host_params.h"
+
+#include <memory>
+
+namespace {
+
+template <int NT>
+void run_exact(const rgs_params &p, const rgs::RunArgs &A) {
+    auto W = std::make_unique<rgs::WarpSlice<double, NT>>();
+    const rgs::DevParams<double> P = rgs::make_dev_params<double>(p);
+    emu::run_warp([&](int lane) { rgs::rollout_exact_warp<NT>(P, A, W.get(), lane, 0, 1); });
+}
+
+template <typename T, int NT>
+void run_fast(const rgs_params &p, const rgs::RunArgs &A) {
+    auto W = std::make_unique<rgs::WarpSlice<T, NT>>();
+    auto tab = std::make_unique<rgs::FastTables<T>>();
+    const rgs::FastParams<T> P = rgs::make_fast_params<T>(p);
+    for (int ty = 0; ty < 2; ++ty)
+        for (int i = 0; i < rgs::kCols; ++i) { tab->g[ty][i] = P.tab_g[ty][i]; tab->k[ty][i] = P.tab_k[ty][i]; }
+    emu::run_warp([&](int lane) { rgs::rollout_fast_warp<T, NT>(P, A, W.get(), tab.get(), lane, 0, 1); });
+}
+
+template <int NT>
+void dispatch(const rgs_params &p, const rgs::RunArgs &A) {
+    if (p.mode == RGS_MODE_EXACT_F64) run_exact<NT>(p, A);
+    else if (p.mode == RGS_MODE_FAST_F32) run_fast<float, NT>(p, A);
+    else run_fast<double, NT>(p, A);
+}
+
+}  // namespace
+
+extern "C" int emu_rollout(const rgs_params *p, int64_t n_games, double *state, double *clock, double *damage,
+                           long long *events, const void *actions, int64_t n_act, int64_t hold, int64_t act_game_stride,
+                           int64_t n_steps, int64_t log_stride, double *traj, int synth, uint64_t seed,
+                           int64_t first_game, int64_t step0, double u_max) {
+    rgs::RunArgs A{};
+    A.n_games = n_games;
+    A.state = state;
+    A.clock = clock;
+    A.damage = damage;
+    A.events = events;
+    A.actions = actions;
+    A.n_act = n_act;
+    A.hold = hold;
+    A.act_game_stride = act_game_stride;
+    A.n_steps = n_steps;
+    A.log_stride = log_stride;
+    A.traj = traj;
+    A.synth = synth;
+    A.seed = seed;
+    A.first_game = first_game;
+    A.step0 = step0;
+    A.u_max = u_max;
+    switch (p->players_per_team) {
+    case 1: dispatch<1>(*p, A); break;
+    case 2: dispatch<2>(*p, A); break;
+    case 3: dispatch<3>(*p, A); break;
+    case 4: dispatch<4>(*p, A); break;
+    case 7: dispatch<7>(*p, A); break;
+    default: return -1;
+    }
+    return 0;
+}
+
+// host evaluation of the synthetic S0 generators (same Philox code as the device)
+extern "C" void emu_synth(uint64_t seed, int64_t first_game, int64_t n, int n_team, int64_t n_act, double u_max,
+                          double *x0_ball, double *actions) {
+    for (int64_t g = 0; g < n; ++g) {
+        const int64_t game = first_game + g;
+        if (x0_ball) {
+            uint32_t o[4];
+            rgs::philox4x32_10((uint32_t)game, (uint32_t)((uint64_t)game >> 32), 0xFFFFFFFFu, 0xFFFFFFFFu, (uint32_t)seed,
+                               (uint32_t)(seed >> 32), o);
+            x0_ball[4 * g + 0] = rgs::sym_uniform(o[0], 4.0);
+            x0_ball[4 * g + 1] = rgs::sym_uniform(o[1], 2.0);
+            x0_ball[4 * g + 2] = rgs::sym_uniform(o[2], 3.0);
+            x0_ball[4 * g + 3] = rgs::sym_uniform(o[3], 3.0);
+        }
+        if (actions)
+            for (int64_t a = 0; a < n_act; ++a)
+                for (int c = 0; c < 4 * n_team; ++c)
+                    actions[(g * n_act + a) * 4 * n_team + c] = rgs::synth_action(seed, game, a, c, u_max);
+    }
+}

@@ -1,0 +1,200 @@
+"""Test-side helpers: ctypes loaders for the CHECKERS (oracle port, compiled reference, warp
+emulator build of the kernel bodies) and the shared synthetic "S0" input generator.
+
+Nothing here is imported by the product package (robo_game_sim_b200 / robo_game_py).
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+import sys  # noqa: E402
+
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+EMU_DIR = os.path.join(ROOT, "tests", "emu")
+
+N_EVENTS = 16
+EV = dict(GOALS_A=0, GOALS_B=1, WALL_UP=2, WALL_DOWN=3, WALL_RIGHT=4, WALL_LEFT=5, PLAYER_PLAYER=6, PLAYER_PUCK=7,
+          DISCARDED=8, LOOP_ITERS=9, LIVE_STEPS=10, DECIDED_STEP=11, COUNTER_LIMIT=12, BASE_CLAMP=13, HASH=14,
+          OVERLAP_FIXES=15)
+
+MODE_EXACT_F64, MODE_FAST_F32, MODE_FAST_F64 = 64, 32, 65
+
+
+class OrcParams(C.Structure):
+    _fields_ = [("dt", C.c_double), ("winning_score", C.c_int32), ("players_per_team", C.c_int32),
+                ("tau_puck", C.c_double), ("tau_player", C.c_double), ("player_mass", C.c_double),
+                ("puck_mass", C.c_double), ("arena_x", C.c_double), ("arena_y", C.c_double),
+                ("player_radius", C.c_double), ("puck_radius", C.c_double), ("goal_height", C.c_double)]
+
+
+class RgsParams(C.Structure):
+    _fields_ = [("dt", C.c_double), ("winning_score", C.c_int32), ("players_per_team", C.c_int32),
+                ("noise", C.c_double), ("tau_puck", C.c_double), ("tau_player", C.c_double),
+                ("player_mass", C.c_double), ("puck_mass", C.c_double), ("arena_x", C.c_double),
+                ("arena_y", C.c_double), ("player_radius", C.c_double), ("puck_radius", C.c_double),
+                ("goal_height", C.c_double), ("mode", C.c_int32), ("reserved", C.c_int32)]
+
+
+def _ptr(a, ct=C.c_double):
+    return None if a is None else a.ctypes.data_as(C.POINTER(ct))
+
+
+_cache = {}
+
+
+def _make(target_dir, *args):
+    subprocess.run(["make", "-C", target_dir, *args], check=True, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE)
+
+
+def oracle_lib():
+    """Plain-C restatement (oracle/gamesim_oracle.c), built on demand with gcc."""
+    if "orc" not in _cache:
+        path = os.path.join(ORACLE_DIR, "liboracle_gamesim.so")
+        _make(ORACLE_DIR, "port")
+        lib = C.CDLL(path)
+        lib.orc_default_params.argtypes = [C.POINTER(OrcParams)]
+        lib.orc_reset_state.argtypes = [C.POINTER(OrcParams), C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        lib.orc_rollout.restype = C.c_int
+        lib.orc_rollout.argtypes = [C.POINTER(OrcParams), C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_double),
+                                    C.POINTER(C.c_double), C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int64,
+                                    C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_double), C.c_int32]
+        lib.orc_log_record.argtypes = [C.POINTER(C.c_double), C.c_double, C.POINTER(C.c_double), C.c_int,
+                                       C.POINTER(C.c_double)]
+        _cache["orc"] = lib
+    return _cache["orc"]
+
+
+def ref_lib():
+    """UNMODIFIED reference GameSim compiled in place (oracle/_ref); None when neither the
+    reference tree nor a prebuilt library is present."""
+    if "ref" not in _cache:
+        path = os.path.join(ORACLE_DIR, "_ref", "libref_gamesim.so")
+        if os.path.exists("/root/reference/src/GameSim.cpp"):
+            _make(ORACLE_DIR, "ref")
+        if not os.path.exists(path):
+            _cache["ref"] = None
+            return None
+        lib = C.CDLL(path)
+        lib.ref_create.restype = C.c_void_p
+        lib.ref_destroy.argtypes = [C.c_void_p]
+        lib.ref_reset.argtypes = [C.c_void_p, C.c_double, C.c_int, C.POINTER(C.c_double), C.c_double, C.c_int,
+                                  C.c_char_p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double,
+                                  C.POINTER(C.c_double)]
+        lib.ref_undecided.argtypes = [C.c_void_p]
+        lib.ref_undecided.restype = C.c_int
+        lib.ref_run.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        lib.ref_time.argtypes = [C.c_void_p]
+        lib.ref_time.restype = C.c_double
+        lib.ref_damage.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        lib.ref_flush_log.argtypes = [C.c_void_p]
+        lib.ref_rollout.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int64, C.POINTER(C.c_double),
+                                    C.POINTER(C.c_double)]
+        lib.ref_rollout_batch.argtypes = [C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_int,
+                                          C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_int64, C.c_double,
+                                          C.c_double, C.c_double, C.c_double, C.POINTER(C.c_double)]
+        _cache["ref"] = lib
+    return _cache["ref"]
+
+
+def emu_lib():
+    """g++ build of the kernel-body headers on the fiber warp emulator (tests/emu)."""
+    if "emu" not in _cache:
+        _make(EMU_DIR)
+        lib = C.CDLL(os.path.join(EMU_DIR, "librgs_emu.so"))
+        lib.emu_rollout.restype = C.c_int
+        lib.emu_rollout.argtypes = [C.POINTER(RgsParams), C.c_int64, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                    C.POINTER(C.c_double), C.POINTER(C.c_int64), C.c_void_p, C.c_int64, C.c_int64,
+                                    C.c_int64, C.c_int64, C.c_int64, C.POINTER(C.c_double), C.c_int, C.c_uint64,
+                                    C.c_int64, C.c_int64, C.c_double]
+        lib.emu_synth.argtypes = [C.c_uint64, C.c_int64, C.c_int64, C.c_int, C.c_int64, C.c_double,
+                                  C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        _cache["emu"] = lib
+    return _cache["emu"]
+
+
+def default_params(n_team=2, winning_score=3, mode=MODE_EXACT_F64, **kw):
+    d = dict(dt=0.05, winning_score=winning_score, players_per_team=n_team, noise=0.0, tau_puck=0.1, tau_player=0.5,
+             player_mass=1.0, puck_mass=0.5, arena_x=10.0, arena_y=5.0, player_radius=0.2, puck_radius=0.175,
+             goal_height=1.0, mode=mode, reserved=0)
+    d.update(kw)
+    return d
+
+
+def rgs_params(d):
+    return RgsParams(**d)
+
+
+def orc_params(d):
+    return OrcParams(**{k: d[k] for k, _ in OrcParams._fields_})
+
+
+from robo_game_sim_b200.synth_np import synth_inputs  # noqa: E402,F401  (numpy S0 generator)
+
+
+def oracle_reset(pd, x0_ball):
+    """[n, 2+4E] initial states for pucks x0_ball [n,4] (GameSim::reset)."""
+    lib = oracle_lib()
+    p = orc_params(pd)
+    n = x0_ball.shape[0]
+    E = 2 * pd["players_per_team"] + 1
+    out = np.zeros((n, 2 + 4 * E))
+    x0 = np.ascontiguousarray(x0_ball, dtype=np.float64)
+    for g in range(n):
+        lib.orc_reset_state(C.byref(p), _ptr(x0[g]), _ptr(out[g]))
+    return out
+
+
+def oracle_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, events=None, traj=False, threads=8):
+    """Oracle port over a batch.  actions [n, n_act, 2n, 2] (or [n_act, 2n, 2] shared).  Returns dict."""
+    lib = oracle_lib()
+    p = orc_params(pd)
+    n = state.shape[0]
+    nt = pd["players_per_team"]
+    state = np.array(state, dtype=np.float64, order="C")
+    t = np.zeros(n) if t is None else np.array(t, dtype=np.float64)
+    damage = np.zeros((n, 4 * nt * nt)) if damage is None else np.array(damage, dtype=np.float64)
+    events = np.zeros((n, N_EVENTS), dtype=np.int64) if events is None else np.array(events, dtype=np.int64)
+    actions = np.ascontiguousarray(actions, dtype=np.float64)
+    shared = actions.ndim == 3
+    n_act = actions.shape[0] if shared else actions.shape[1]
+    stride = 0 if shared else n_act * 4 * nt
+    tr = np.zeros((n, n_steps, state.shape[1])) if traj else None
+    rc = lib.orc_rollout(C.byref(p), n, n_steps, hold, _ptr(state), _ptr(t), _ptr(damage), _ptr(actions), n_act, stride,
+                         _ptr(events, C.c_int64), _ptr(tr), threads)
+    assert rc == 0
+    return dict(state=state, t=t, damage=damage, events=events, traj=tr)
+
+
+def emu_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, events=None, log_stride=0, synth=None):
+    """The product's kernel body stepped on the CPU warp emulator (one warp, games in sequence)."""
+    lib = emu_lib()
+    p = rgs_params(pd)
+    n = state.shape[0]
+    nt = pd["players_per_team"]
+    state = np.array(state, dtype=np.float64, order="C")
+    t = np.zeros(n) if t is None else np.array(t, dtype=np.float64)
+    damage = np.zeros((n, 4 * nt * nt)) if damage is None else np.array(damage, dtype=np.float64)
+    events = np.zeros((n, N_EVENTS), dtype=np.int64) if events is None else np.array(events, dtype=np.int64)
+    traj = None
+    if log_stride:
+        traj = np.zeros((n, n_steps // log_stride, 1 + state.shape[1] + 4 * nt * nt))
+    if synth is not None:
+        seed, first_game, step0, u_max = synth
+        rc = lib.emu_rollout(C.byref(p), n, _ptr(state), _ptr(t), _ptr(damage), _ptr(events, C.c_int64), None, 1, hold,
+                             0, n_steps, log_stride, _ptr(traj), 1, seed, first_game, step0, u_max)
+    else:
+        dt = np.float32 if pd["mode"] == MODE_FAST_F32 else np.float64
+        actions = np.ascontiguousarray(actions, dtype=dt)
+        shared = actions.ndim == 3
+        n_act = actions.shape[0] if shared else actions.shape[1]
+        stride = 0 if shared else n_act * 4 * nt
+        rc = lib.emu_rollout(C.byref(p), n, _ptr(state), _ptr(t), _ptr(damage), _ptr(events, C.c_int64),
+                             actions.ctypes.data_as(C.c_void_p), n_act, hold, stride, n_steps, log_stride, _ptr(traj),
+                             0, 0, 0, 0, 0.0)
+    assert rc == 0
+    return dict(state=state, t=t, damage=damage, events=events, traj=traj)

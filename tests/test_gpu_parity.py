@@ -1,0 +1,300 @@
+"""GPU suite (-m gpu): the CUDA kernels, called through the C ABI (robo_game_sim_b200 -> librgs_b200.so),
+against the oracle on the same seeded inputs, against the committed golden fixtures, and -- at
+BASELINE.json's full sizes -- through size-independent properties.
+
+Bars: fp64 parity mode (K1) bit-exact on every state double, clock, damage and event record;
+fast fp64 (K2 formulation) event-identical except where the reference's own absolute-time rounding
+decides; fast fp32 (K2) statistically equal to the oracle's Monte Carlo distributions.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import rgs_testlib as tl
+from conftest import GOLDEN_CASES
+
+pytestmark = pytest.mark.gpu
+
+torch = pytest.importorskip("torch")
+
+
+@pytest.fixture(scope="module")
+def rgs():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import robo_game_sim_b200
+
+    return robo_game_sim_b200
+
+
+def _gpu_rollout(rgs, mode, pd, x0, acts, steps, hold, log_stride=0):
+    n = x0.shape[0]
+    kw = {k: pd[k] for k in ("dt", "winning_score", "tau_puck", "tau_player", "player_mass", "puck_mass")}
+    sim = rgs.BatchedGameSim(n, mode=mode, players_per_team=pd["players_per_team"], **kw)
+    sim.reset(x0_ball=torch.from_numpy(x0).cuda())
+    a = torch.from_numpy(np.ascontiguousarray(acts)).to(sim.action_dtype).cuda()
+    traj = sim.run(a, n_steps=steps, hold=hold, log_stride=log_stride)
+    out = dict(state=sim.state().cpu().numpy(), t=sim.time().cpu().numpy(), damage=sim.damage().cpu().numpy().reshape(n, -1),
+               events=sim.events().cpu().numpy(), stats=sim.stats().cpu().numpy(),
+               traj=None if traj is None else traj.cpu().numpy())
+    return sim, out
+
+
+def _assert_bit_exact(o, g):
+    assert np.array_equal(o["state"], g["state"])
+    assert np.array_equal(o["events"], g["events"])
+    assert np.array_equal(o["damage"], g["damage"])
+    assert np.array_equal(o["t"], g["t"])
+
+
+# ------------------------------------------------------------------ K1: fp64 parity mode
+def test_exact_bit_exact_s0_2v2(rgs):
+    n, steps, hold = 4096, 200, 10
+    pd = tl.default_params(winning_score=3)
+    x0, acts = tl.synth_inputs(42, 0, n, 2, steps // hold)
+    o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), acts, steps, hold)
+    _, g = _gpu_rollout(rgs, "exact", pd, x0, acts, steps, hold)
+    _assert_bit_exact(o, g)
+    assert o["events"][:, 2:8].sum() > 1e5 and o["events"][:, :2].sum() > 50   # collisions and goals are exercised
+
+
+@pytest.mark.parametrize("n_team,n,steps", [(1, 256, 100), (4, 512, 100), (7, 256, 60)])
+def test_exact_bit_exact_nvn(rgs, n_team, n, steps):
+    """BASELINE configs[3]: 4v4 and 7v7 (O(n^2) pair stress); oracle = the n-v-n restatement."""
+    pd = tl.default_params(n_team=n_team, winning_score=3)
+    x0, acts = tl.synth_inputs(43, 0, n, n_team, steps // 10)
+    o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), acts, steps, 10)
+    _, g = _gpu_rollout(rgs, "exact", pd, x0, acts, steps, 10)
+    _assert_bit_exact(o, g)
+
+
+@pytest.mark.parametrize("name", GOLDEN_CASES)
+def test_exact_golden_cases(rgs, golden, name):
+    pd = tl.default_params(winning_score=int(golden[name + "/winning_score"]), tau_puck=float(golden[name + "/tau_puck"]))
+    acts = golden[name + "/actions"].reshape(1, -1, 4, 2)
+    _, g = _gpu_rollout(rgs, "exact", pd, golden[name + "/x0"][None, :], acts, acts.shape[1], 1, log_stride=1)
+    assert np.array_equal(g["traj"][0, :, 1:23], golden[name + "/states"])
+    assert g["t"][0] == float(golden[name + "/t"])
+    assert np.array_equal(g["damage"][0], golden[name + "/damage"])
+
+
+def test_exact_golden_s0(rgs, golden):
+    pd = tl.default_params(winning_score=3)
+    _, g = _gpu_rollout(rgs, "exact", pd, golden["s0/x0"], golden["s0/actions"], 400, 10, log_stride=1)
+    assert np.array_equal(g["state"], golden["s0/final"])
+    assert np.array_equal(g["t"], golden["s0/t"])
+    assert np.array_equal(g["damage"], golden["s0/damage"])
+    assert np.array_equal(g["traj"][:3, :, 1:23], golden["s0/traj3"])
+
+
+def test_collision_cases_batched_1e5(rgs, golden):
+    """BASELINE configs[2]: the bounce-kick / wall-contact / KAT cases replicated 10^5 x with
+    per-replica jitter ~U(-1e-3,1e-3) on the puck start, 400 steps, fp64 parity mode.  Full size on
+    the GPU; the oracle checks a strided sample of 2000 replicas bit for bit, the rest through
+    properties (finite states, event totals consistent with the statistics vector)."""
+    names = ["kat1_goal", "kat2_wall_up", "kat4_head_on", "bounce_kick_up", "bounce_kick_down", "wall_contacts"]
+    n, steps = 100_000, 400
+    rng = np.random.default_rng(7)
+    for tau in (0.1, 1.0):
+        sel = [nm for nm in names if float(golden[nm + "/tau_puck"]) == tau]
+        case = rng.integers(0, len(sel), n)
+        x0 = np.stack([golden[sel[c] + "/x0"] for c in case]) + np.concatenate(
+            [rng.uniform(-1e-3, 1e-3, (n, 2)), np.zeros((n, 2))], axis=1)
+        uniq = np.stack([np.resize(golden[nm + "/actions"], (steps, 8)) for nm in sel])     # [cases, steps, 8]
+        pd = tl.default_params(winning_score=3, tau_puck=tau)
+        # per-game command tensors are case-indexed: build [n, steps, 4, 2] lazily on the device
+        sim = rgs.BatchedGameSim(n, mode="exact", winning_score=3, tau_puck=tau)
+        sim.reset(x0_ball=torch.from_numpy(x0).cuda())
+        acts_dev = torch.from_numpy(uniq).cuda()[torch.from_numpy(case).cuda()].reshape(n, steps, 4, 2).contiguous()
+        sim.run(acts_dev, n_steps=steps, hold=1)
+        st, ev, dmg, t = (x.cpu().numpy() for x in (sim.state(), sim.events(), sim.damage(), sim.time()))
+        assert np.isfinite(st).all()
+        idx = np.arange(0, n, n // 2000)
+        o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0[idx]), uniq[case[idx]].reshape(len(idx), steps, 4, 2), steps, 1)
+        assert np.array_equal(o["state"], st[idx]) and np.array_equal(o["events"], ev[idx])
+        assert np.array_equal(o["damage"], dmg.reshape(n, -1)[idx]) and np.array_equal(o["t"], t[idx])
+        stats = sim.stats().cpu().numpy()
+        assert stats[0] == n and np.array_equal(stats[8:22], ev[:, :14].sum(0))
+
+
+def test_drop_in_gamesim_matches_reference_step_by_step(rgs, tmp_path):
+    """robo_game_py.GameSim (reset / priming run / run loop, as py/MonteCarlo.py:28-45 drives it) against
+    the compiled reference (or the oracle port) including the 29-double binary log."""
+    from robo_game_py import GameSim
+
+    steps = 120
+    x0, acts = tl.synth_inputs(5, 3, 1, 2, steps // 10)
+    a_steps = np.repeat(acts[0].reshape(-1, 8), 10, axis=0)
+    sim = GameSim()
+    assert repr(sim) == "GameSim Object"
+    logname = str(tmp_path / "mine.log")
+    s = sim.reset(0.05, 3, x0[0], 0.0, True, logname, 1, 0.1, 0.5, 1.0, 0.5)
+    assert s.dtype == np.float64 and s.shape == (22,)
+    mine = [sim.run(np.zeros(2), np.zeros(2), np.zeros(2), np.zeros(2))]
+    for k in range(steps):
+        mine.append(sim.run(a_steps[k, 0:2], a_steps[k, 2:4], list(a_steps[k, 4:6]), a_steps[k, 6:8].reshape(2, 1)))
+        assert sim.undecided() == bool(mine[-1][0] < 3 and mine[-1][1] < 3)
+    sim.reset(0.05, 3, x0[0], 0.0, False, "")        # 6-argument form of run_sim.py:43; closes the log
+    mine = np.array(mine)
+    full = np.concatenate([np.zeros((1, 8)), a_steps])
+    lib = tl.ref_lib()
+    if lib is not None:
+        dp = C.POINTER(C.c_double)
+        h = lib.ref_create()
+        ref_log = str(tmp_path / "ref.log").encode()
+        lib.ref_reset(h, 0.05, 3, x0[0].ctypes.data_as(dp), 0.0, 1, ref_log, 1, 0.1, 0.5, 1.0, 0.5, None)
+        st = np.zeros((steps + 1, 22))
+        lib.ref_rollout(h, np.ascontiguousarray(full).ctypes.data_as(dp), steps + 1, st.ctypes.data_as(dp), None)
+        lib.ref_destroy(h)       # flushes and closes the reference log
+        assert np.array_equal(mine, st)
+        assert open(logname, "rb").read() == open(ref_log.decode(), "rb").read()
+    else:
+        pd = tl.default_params(winning_score=3)
+        o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), full.reshape(1, -1, 4, 2), steps + 1, 1, traj=True)
+        assert np.array_equal(mine, o["traj"][0])
+    rec = np.fromfile(logname).reshape(-1, 29)
+    assert rec.shape[0] == steps + 1 and np.allclose(rec[:, 0], 0.05 * np.arange(1, steps + 2))
+    assert np.array_equal(rec[:, 3:5], mine[:, 2:4])
+    with pytest.raises(TypeError):
+        sim.run(np.zeros(3), np.zeros(2), np.zeros(2), np.zeros(2))
+    with pytest.raises(TypeError):
+        sim.reset(0.05, 3)
+
+
+def test_resume_synth_stats_and_host_entry(rgs):
+    """Rollout boundary = checkpoint; on-chip S0 commands == tensor commands; K4 == numpy; the
+    host-buffer entry point == the device-tensor entry point."""
+    n, steps, hold = 3000, 100, 10
+    pd = tl.default_params(winning_score=2)
+    x0, acts = tl.synth_inputs(9, 50, n, 2, steps // hold)
+    sim, g = _gpu_rollout(rgs, "exact", pd, x0, acts, steps, hold)
+    # device S0 generator == numpy generator
+    dx0, dacts = rgs.synth_inputs(n, steps // hold, seed=9, first_game=50)
+    assert np.array_equal(dx0.cpu().numpy(), x0) and np.array_equal(dacts.cpu().numpy(), acts)
+    # 2 x 50 steps with on-chip commands
+    sim2 = rgs.BatchedGameSim(n, mode="exact", winning_score=2)
+    sim2.reset(x0_ball=dx0)
+    sim2.run_synth(9, 50, hold=hold, first_game=50, step0=0)
+    sim2.run_synth(9, 50, hold=hold, first_game=50, step0=50)
+    assert np.array_equal(sim2.state().cpu().numpy(), g["state"])
+    assert np.array_equal(sim2.events().cpu().numpy(), g["events"])
+    # restore from a full-state checkpoint
+    sim3 = rgs.BatchedGameSim(n, mode="exact", winning_score=2)
+    sim3.reset(state0=torch.from_numpy(tl.oracle_reset(pd, x0)).cuda())
+    sim3.run(dacts, n_steps=steps, hold=hold)
+    assert np.array_equal(sim3.state().cpu().numpy(), g["state"])
+    # statistics vector
+    st, ev, s = g["state"], g["events"], g["stats"]
+    assert s[0] == n and s[1] == (st[:, 0] >= 2).sum() and s[2] == ((st[:, 1] >= 2) & (st[:, 0] < 2)).sum()
+    assert s[3] == ((st[:, 0] < 2) & (st[:, 1] < 2)).sum() and s[1] + s[2] + s[3] == n
+    assert np.array_equal(s[8:22], ev[:, :14].sum(0))
+    hist = np.zeros((5, 5), dtype=np.int64)
+    np.add.at(hist, (np.minimum(st[:, 0], 4).astype(int), np.minimum(st[:, 1], 4).astype(int)), 1)
+    assert np.array_equal(s[32:57].reshape(5, 5), hist)
+    # host-buffer entry point
+    hs, he, hst = sim.run_host(x0, acts, steps, hold=hold)
+    assert np.array_equal(hs, g["state"]) and np.array_equal(he, g["events"]) and np.array_equal(hst, g["stats"])
+    # frozen games do not advance their clock
+    dec = ev[:, tl.EV["DECIDED_STEP"]] > 0
+    assert dec.any() and np.allclose(g["t"][dec], 0.05 * ev[dec, tl.EV["DECIDED_STEP"]])
+
+
+# ------------------------------------------------------------------ K2: throughput formulation
+def test_fast64_tracks_oracle(rgs):
+    n, steps, hold = 4096, 100, 10
+    pd = tl.default_params(winning_score=3)
+    x0, acts = tl.synth_inputs(42, 0, n, 2, steps // hold)
+    o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), acts, steps, hold)
+    _, g = _gpu_rollout(rgs, "fast64", pd, x0, acts, steps, hold)
+    same = o["events"][:, 14] == g["events"][:, 14]
+    assert same.mean() > 0.95
+    assert np.array_equal(o["events"][same][:, :14], g["events"][same][:, :14])
+    assert np.median(np.abs(o["state"] - g["state"])[same].max(1)) < 1e-8
+    # and the emulator build of the same source gives the same bits as the GPU
+    e = tl.emu_rollout(dict(pd, mode=tl.MODE_FAST_F64), tl.oracle_reset(pd, x0[:64]), acts[:64], steps, hold)
+    assert np.array_equal(e["state"], g["state"][:64]) and np.array_equal(e["events"], g["events"][:64])
+
+
+def test_fast32_statistics_match_oracle(rgs):
+    """fp32 throughput mode vs the oracle's Monte Carlo distributions on 20000 S0 games x 200 steps:
+    per-step event rates within 3 %, goal totals within 5 sigma (Poisson), identical live-step counts
+    for undecided games, and the one-step error on contact-free steps below 1e-5."""
+    n, steps, hold = 20000, 200, 10
+    pd = tl.default_params(winning_score=4)
+    x0, acts = tl.synth_inputs(2027, 0, n, 2, steps // hold)
+    o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), acts, steps, hold)
+    _, g = _gpu_rollout(rgs, "fast", pd, x0, acts.astype(np.float32), steps, hold)
+    eo, eg = o["events"].sum(0).astype(float), g["events"].sum(0).astype(float)
+    for k in ("WALL_UP", "WALL_DOWN", "WALL_RIGHT", "WALL_LEFT", "PLAYER_PUCK"):
+        assert abs(eg[tl.EV[k]] - eo[tl.EV[k]]) / eo[tl.EV[k]] < 0.03, k
+    # player-player counts are dominated by a few jammed games (heavy tail): compare the per-game median rate
+    assert abs(np.median(g["events"][:, 6]) - np.median(o["events"][:, 6])) <= 1
+    goals_o, goals_g = eo[0] + eo[1], eg[0] + eg[1]
+    assert abs(goals_g - goals_o) < 5 * np.sqrt(goals_o + 1)
+    assert abs((g["state"][:, 0] > g["state"][:, 1]).mean() - (o["state"][:, 0] > o["state"][:, 1]).mean()) < 0.01
+    # emulator (g++) == GPU, bit for bit, also in fp32 (explicit FMAs, -fmad=false)
+    e = tl.emu_rollout(dict(pd, mode=tl.MODE_FAST_F32), tl.oracle_reset(pd, x0[:48]), acts[:48], steps, hold)
+    assert np.array_equal(e["state"], g["state"][:48]) and np.array_equal(e["events"], g["events"][:48])
+
+
+def test_fast32_full_size_properties(rgs):
+    """BASELINE configs[1] size on one GPU (10^6 games x 200 steps): determinism, independence of the
+    batch composition (a game's result does not depend on which other games share the launch),
+    y-mirror symmetry of the physics, and event totals consistent with the statistics vector."""
+    n, steps, hold = 1_000_000, 200, 10
+    sim = rgs.BatchedGameSim(n, mode="fast", winning_score=4)
+    x0, acts = rgs.synth_inputs(n, steps // hold, seed=11, dtype=torch.float32)
+    sim.reset(x0_ball=x0)
+    sim.run(acts, n_steps=steps, hold=hold)
+    st, ev, stats = sim.state(), sim.events(), sim.stats()
+    assert torch.isfinite(st).all()
+    assert int(stats[0]) == n and torch.equal(stats[8:22], ev[:, :14].sum(0))
+    assert int(ev[:, 10].min()) > 0 and int(ev[:, 10].max()) == steps
+    sim.reset(x0_ball=x0)
+    sim.run(acts, n_steps=steps, hold=hold)
+    assert torch.equal(sim.state(), st) and torch.equal(sim.events(), ev)            # deterministic
+    lo, cnt = 123_457, 10_000
+    sub = rgs.BatchedGameSim(cnt, mode="fast", winning_score=4)
+    sub.reset(x0_ball=x0[lo:lo + cnt].contiguous())
+    sub.run(acts[lo:lo + cnt].contiguous(), n_steps=steps, hold=hold)
+    assert torch.equal(sub.state(), st[lo:lo + cnt]) and torch.equal(sub.events(), ev[lo:lo + cnt])
+    # mirror y -> -y of puck start and of every command: players start at +-1.25, so A1<->A2, B1<->B2 swap roles
+    m = 100_000
+    mx0 = x0[:m].clone()
+    mx0[:, 1] *= -1
+    mx0[:, 3] *= -1
+    ma = acts[:m].clone()[:, :, [1, 0, 3, 2], :]
+    ma[..., 1] *= -1
+    mir = rgs.BatchedGameSim(m, mode="fast", winning_score=4)
+    mir.reset(x0_ball=mx0)
+    mir.run(ma.contiguous(), n_steps=steps, hold=hold)
+    mev, mst = mir.events(), mir.state()
+    same_goals = (mev[:, :2] == ev[:m, :2]).all(1).float().mean().item()
+    assert same_goals > 0.98            # identical up to body-order tie-breaks in jams
+    assert abs(int(mev[:, 2].sum()) - int(ev[:m, 3].sum())) / max(1, int(ev[:m, 3].sum())) < 0.02   # UP <-> DOWN
+
+
+def test_monte_carlo_batched_harness(rgs, tmp_path):
+    import types
+
+    mc = types.SimpleNamespace(num_runs=5000, T=10.0, dt=0.05, winning_score=4, x0_ball=np.array([-1.0, 0, 0, 0]),
+                               noise_stdev=0.0, tau_puck=0.1, tau_player=0.5, player_mass=1.0, puck_mass=0.5,
+                               log_prefix=str(tmp_path / "mc"))
+    out = rgs.monte_carlo_batched(mc, mode="exact", seed=3)
+    assert out["games"] == 5000 and out["n_steps"] == 200
+    assert out["live_steps"] <= 5000 * 201 and out["live_steps"] > 5000 * 150
+    assert len(open(os.path.join(mc.log_prefix, "configuration.txt")).read().splitlines()) == 13
+    # deterministic open-loop commands shared by all runs: every run is the same game (noise = 0)
+    acts = np.zeros((20, 4, 2))
+    acts[:, 0] = (5.0, -3.0)
+    out2 = rgs.monte_carlo_batched(mc, actions=acts, mode="exact", hold=10)
+    pd = tl.default_params(winning_score=4)
+    full = np.concatenate([np.zeros((1, 4, 2)), np.repeat(acts, 10, axis=0)])
+    o = tl.oracle_rollout(pd, tl.oracle_reset(pd, mc.x0_ball[None, :]), full, 201, 1)
+    assert out2["player_puck"] == 5000 * o["events"][0, 7] and out2["wall_up"] == 5000 * o["events"][0, 2]
+    # closed loop through a Python policy (host in the loop, like the reference harness)
+    mc.num_runs, mc.T = 64, 1.0
+    out3 = rgs.monte_carlo_batched(mc, policy=lambda s: torch.zeros((s.shape[0], 4, 2), device=s.device), mode="fast")
+    assert out3["games"] == 64 and out3["live_steps"] == 64 * 21
