@@ -167,28 +167,28 @@ def test_resume_synth_stats_and_host_entry(rgs):
     """Rollout boundary = checkpoint; on-chip S0 commands == tensor commands; K4 == numpy; the
     host-buffer entry point == the device-tensor entry point."""
     n, steps, hold = 3000, 100, 10
-    pd = tl.default_params(winning_score=2)
+    pd = tl.default_params(winning_score=1)
     x0, acts = tl.synth_inputs(9, 50, n, 2, steps // hold)
     sim, g = _gpu_rollout(rgs, "exact", pd, x0, acts, steps, hold)
     # device S0 generator == numpy generator
     dx0, dacts = rgs.synth_inputs(n, steps // hold, seed=9, first_game=50)
     assert np.array_equal(dx0.cpu().numpy(), x0) and np.array_equal(dacts.cpu().numpy(), acts)
     # 2 x 50 steps with on-chip commands
-    sim2 = rgs.BatchedGameSim(n, mode="exact", winning_score=2)
+    sim2 = rgs.BatchedGameSim(n, mode="exact", winning_score=1)
     sim2.reset(x0_ball=dx0)
     sim2.run_synth(9, 50, hold=hold, first_game=50, step0=0)
     sim2.run_synth(9, 50, hold=hold, first_game=50, step0=50)
     assert np.array_equal(sim2.state().cpu().numpy(), g["state"])
     assert np.array_equal(sim2.events().cpu().numpy(), g["events"])
     # restore from a full-state checkpoint
-    sim3 = rgs.BatchedGameSim(n, mode="exact", winning_score=2)
+    sim3 = rgs.BatchedGameSim(n, mode="exact", winning_score=1)
     sim3.reset(state0=torch.from_numpy(tl.oracle_reset(pd, x0)).cuda())
     sim3.run(dacts, n_steps=steps, hold=hold)
     assert np.array_equal(sim3.state().cpu().numpy(), g["state"])
     # statistics vector
     st, ev, s = g["state"], g["events"], g["stats"]
-    assert s[0] == n and s[1] == (st[:, 0] >= 2).sum() and s[2] == ((st[:, 1] >= 2) & (st[:, 0] < 2)).sum()
-    assert s[3] == ((st[:, 0] < 2) & (st[:, 1] < 2)).sum() and s[1] + s[2] + s[3] == n
+    assert s[0] == n and s[1] == (st[:, 0] >= 1).sum() and s[2] == ((st[:, 1] >= 1) & (st[:, 0] < 1)).sum()
+    assert s[3] == ((st[:, 0] < 1) & (st[:, 1] < 1)).sum() and s[1] + s[2] + s[3] == n
     assert np.array_equal(s[8:22], ev[:, :14].sum(0))
     hist = np.zeros((5, 5), dtype=np.int64)
     np.add.at(hist, (np.minimum(st[:, 0], 4).astype(int), np.minimum(st[:, 1], 4).astype(int)), 1)
