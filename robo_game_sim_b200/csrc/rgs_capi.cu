@@ -10,6 +10,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -68,6 +69,7 @@ struct rgs_batch {
     int64_t n_games = 0;
     rgs_params p{};
     int n_team = 2, E = 5, srec = 22, dmg_rec = 16;
+    bool warp_k2 = false;  // RGS_K2_WARP=1: the superseded warp-per-game throughput kernel (A/B measurements only)
     double *state = nullptr, *clock = nullptr, *damage = nullptr;
     long long *events = nullptr, *stats = nullptr;
     // staging for rgs_batch_run_host
@@ -121,10 +123,12 @@ int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64
         e = rgs::launch_rollout_exact(b->n_team, rgs::make_dev_params<double>(b->p), A, stream, b->sm_count);
         break;
     case RGS_MODE_FAST_F32:
-        e = rgs::launch_rollout_fast_f32(b->n_team, b->p, A, stream, b->sm_count);
+        e = b->warp_k2 ? rgs::launch_rollout_fast_f32(b->n_team, b->p, A, stream, b->sm_count)
+                       : rgs::launch_rollout_lane_f32(b->n_team, b->p, A, stream, b->sm_count);
         break;
     default:
-        e = rgs::launch_rollout_fast_f64(b->n_team, b->p, A, stream, b->sm_count);
+        e = b->warp_k2 ? rgs::launch_rollout_fast_f64(b->n_team, b->p, A, stream, b->sm_count)
+                       : rgs::launch_rollout_lane_f64(b->n_team, b->p, A, stream, b->sm_count);
         break;
     }
     if (e != cudaSuccess) return cuda_fail(e, "rollout kernel launch");
@@ -203,6 +207,10 @@ int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_par
     b->E = 2 * b->n_team + 1;
     b->srec = 2 + 4 * b->E;
     b->dmg_rec = 4 * b->n_team * b->n_team;
+    {
+        const char *w = std::getenv("RGS_K2_WARP");
+        b->warp_k2 = w && w[0] == '1';
+    }
     cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
     const size_t n = (size_t)(n_games > 0 ? n_games : 1);
     cudaError_t err = cudaSuccess;

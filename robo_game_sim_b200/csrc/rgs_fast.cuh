@@ -41,6 +41,7 @@ struct FastParams {
     T tab_g[2][kCols];      // R^i
     T tab_k[2][kCols];      // a (1-R^i)/(1-R)
     T lim_x[2], lim_y[2];   // arena/2 - r (folded wall-overlap limits for the register phase)
+    T lim_x_in[2], lim_y_in[2];  // largest value strictly below lim (lane kernel: a corrected body never rests ON the limit)
 };
 
 template <typename T>

@@ -90,6 +90,8 @@ inline FastParams<T> make_fast_params(const rgs_params &p) {
         }
         f.lim_x[ty] = T(p.arena_x / 2.0 - rad[ty]);
         f.lim_y[ty] = T(p.arena_y / 2.0 - rad[ty]);
+        f.lim_x_in[ty] = std::nextafter(f.lim_x[ty], T(0));
+        f.lim_y_in[ty] = std::nextafter(f.lim_y[ty], T(0));
     }
     return f;
 }

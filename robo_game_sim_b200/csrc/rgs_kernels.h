@@ -16,6 +16,10 @@ cudaError_t launch_rollout_exact(int n_team, const DevParams<double> &P, const R
 cudaError_t launch_rollout_fast_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 cudaError_t launch_rollout_fast_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 
+// K2, one lane per game (rgs_lane_kernel.cu): the throughput kernel the FAST modes run
+cudaError_t launch_rollout_lane_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
+cudaError_t launch_rollout_lane_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
+
 // K4: per-batch statistics vector int64[RGS_N_STATS] (rgs_aux_kernels.cu)
 cudaError_t launch_stats(int n_team, int64_t n_games, const double *state, const long long *events, int winning_score,
                          long long *d_stats, cudaStream_t stream, int sm_count);

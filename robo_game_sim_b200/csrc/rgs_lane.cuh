@@ -1,0 +1,696 @@
+// rgs_lane.cuh -- K2 (lane body): fused multi-step rollout in the THROUGHPUT formulation,
+// ONE LANE PER GAME.
+//
+// Why not a warp per game here (K1 keeps that mapping): the first B200 profile of the warp-per-game
+// throughput kernel (profiles/r01_k2_warp_per_game.md) showed 666 warp-instructions per game-step,
+// 45 % of them in a per-column broad phase that finds nothing in 3 steps out of 4, the rest in a
+// serial event path in which 31 lanes idle, and the issue slots 72 % empty on instruction-fetch
+// stalls (78 KB of divergent code).  Games are independent, so the natural SIMT mapping of a huge
+// Monte Carlo batch is game -> lane: every arithmetic instruction does 32 games' worth of work, the
+// broad phase becomes a handful of bounding-interval tests per game-step, and only the games that
+// can touch something enter the narrow phase.
+//
+// Formulation (same event semantics as the reference step, GameSim::updateSim, reference
+// src/GameSim.cpp:126-171: overlap detected at the 50 grid columns, linear back-tracking from
+// column i-1, per-owner events, earliest-first resolution with the stable-sort tie rule, prune +
+// re-scan, one goal per step):
+//   * time is step-relative; the 50-sub-step RK4 chain (:173-217, :70-116) is replaced by its
+//     closed form (see rgs_fast.cuh): i sub-steps are the affine map v_i = u + (v0-u) R^i,
+//     p_i = p0 + u i h + (v0-u) k_i, so NO grid is stored: a body's trajectory inside the step is a
+//     SEGMENT {start column, state at the start column, state at the column before it} plus the
+//     position offsets that correctOverlap (:581-623) added after the start;
+//   * broad phase: the velocity of a segment is monotone between its end values, so the position
+//     stays inside [p + min(0, vmin T), p + max(0, vmax T)]; bodies whose intervals (inflated by the
+//     radii) cannot meet a wall or each other are never column-tested.  The bound is conservative,
+//     so the events found are the ones the full column scan (insertCollisions :360-511) finds;
+//   * narrow phase: flagged (body, wall) and (body, body) ITEMS are marched over the columns with
+//     the one-column affine map; an item's first column with a valid time of impact is folded into
+//     its owner bodies with the reference's candidate order (walls UP, DOWN, RIGHT, LEFT, then the
+//     other bodies in entity order; strict '<' keeps the first);
+//   * events are resolved exactly like K2's warp formulation did (rgs_fast.cuh history): advance
+//     to the impact time with the RK4 polynomial, 1.01 overlap push, elastic impulse, damage,
+//     advance to the next column, correctOverlap on every later column.
+// Deviation kept on purpose (documented in DESIGN.md): only the LAST correctOverlap offset of a
+// body is tracked per column; a third body that re-scans against columns between two earlier
+// offsets of the same step sees the later offset early (affects jammed multi-contact steps only).
+//
+// Everything is plain scalar C++ over a per-game scratch record, so tests/emu compiles the same
+// source with g++ (no warp emulation needed).  All fused multiply-adds are spelled out (fm()).
+#pragma once
+#include "rgs_fast.cuh"
+
+namespace rgs {
+
+// per-game scratch record: word w of game slot s lives at base[w * stride + s] (bank = lane)
+template <typename T, int NT>
+struct LaneScratch {
+    static constexpr int E = 2 * NT + 1;
+    // T words
+    static constexpr int SP = 0;         // [4e+c] state at the segment start column
+    static constexpr int CMD = 4 * E;    // [2e+a] commanded velocity (puck: 0)
+    static constexpr int PRV = 6 * E;    // [4e+c] state at the column before the segment start
+    static constexpr int OFF = 10 * E;   // [4e+{0,1}] total correctOverlap offset, [4e+{2,3}] offset before the last fix
+    static constexpr int BB = 14 * E;    // [4e+{0..3}] bounding interval lo_x, hi_x, lo_y, hi_y of the segment
+    static constexpr int QT = 18 * E;    // [e] queued / candidate event time of owner e
+    static constexpr int NF = 19 * E;
+    // int words
+    static constexpr int CS = 0;         // [e] segment start column
+    static constexpr int FL = E;         // [e] column of the last correctOverlap fix (= CS when none)
+    static constexpr int QI = 2 * E;     // [e] (seq << 12) | (col << 6)... see q_pack
+    static constexpr int NI = 3 * E;
+    T *f;
+    int *i;
+    int stride;
+    RGS_DEV T &F(int w) const { return f[w * stride]; }
+    RGS_DEV int &I(int w) const { return i[w * stride]; }
+};
+
+struct LaneTabEntry32 { float g, k; };
+template <typename T>
+struct LaneTab {   // block-shared coefficient table, [type][j] -> {R^j, a (1-R^j)/(1-R)}
+    T g[2][kCols];
+    T k[2][kCols];
+};
+
+// small fixed-size bitset in registers
+template <int NBITS>
+struct Bits {
+    static constexpr int NW = (NBITS + 31) / 32;
+    unsigned w[NW];
+    RGS_DEV void clear() {
+#pragma unroll
+        for (int k = 0; k < NW; ++k) w[k] = 0u;
+    }
+    RGS_DEV void set(int b) {
+#pragma unroll
+        for (int k = 0; k < NW; ++k)
+            if ((b >> 5) == k) w[k] |= 1u << (b & 31);
+    }
+    RGS_DEV bool any() const {
+        unsigned a = 0u;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) a |= w[k];
+        return a != 0u;
+    }
+    // index of the lowest set bit (removed), -1 when empty
+    RGS_DEV int pop() {
+        int r = -1;
+#pragma unroll
+        for (int k = 0; k < NW; ++k) {
+            if (r < 0 && w[k] != 0u) {
+#ifdef RGS_HOST_EMU
+                const int b = __builtin_ctz(w[k]);
+#else
+                const int b = __ffs((int)w[k]) - 1;
+#endif
+                w[k] &= w[k] - 1u;
+                r = 32 * k + b;
+            }
+        }
+        return r;
+    }
+};
+
+template <typename T>
+RGS_DEV T tmin(T a, T b) { return a < b ? a : b; }
+template <typename T>
+RGS_DEV T tmax(T a, T b) { return a > b ? a : b; }
+
+// broad-phase slack: the bounding intervals are evaluated with different roundings than the
+// column positions, so thresholds are inflated by a few hundred ulps of the arena size
+template <typename T> struct Slack;
+template <> struct Slack<float> { static constexpr float v = 2.0e-4f; };
+template <> struct Slack<double> { static constexpr double v = 1.0e-9; };
+
+template <typename T, int NT>
+struct LaneGame {
+    static constexpr int E = 2 * NT + 1, PK = 2 * NT, NP = 2 * NT, NPAIR = E * (E - 1) / 2;
+    using S = LaneScratch<T, NT>;
+    const FastParams<T> &P;
+    const LaneTab<T> *tab;
+    S s;
+
+    RGS_DEV LaneGame(const FastParams<T> &P_, const LaneTab<T> *tab_, const S &s_) : P(P_), tab(tab_), s(s_) {}
+
+    // state of body e at column c >= CS[e]-1 (position includes the correctOverlap offsets)
+    RGS_DEV void eval(int e, int c, T &px, T &py, T &vx, T &vy) const {
+        const int j = c - s.I(S::CS + e);
+        if (j < 0) {
+            px = s.F(S::PRV + 4 * e); py = s.F(S::PRV + 4 * e + 1); vx = s.F(S::PRV + 4 * e + 2); vy = s.F(S::PRV + 4 * e + 3);
+            return;
+        }
+        const T spx = s.F(S::SP + 4 * e), spy = s.F(S::SP + 4 * e + 1), svx = s.F(S::SP + 4 * e + 2), svy = s.F(S::SP + 4 * e + 3);
+        if (j == 0) { px = spx; py = spy; vx = svx; vy = svy; return; }
+        const int ty = (e == PK);
+        const T ux = s.F(S::CMD + 2 * e), uy = s.F(S::CMD + 2 * e + 1);
+        const T g = tab->g[ty][j], k = tab->k[ty][j], tj = P.d.dt_col * T(j);
+        const T wx = svx - ux, wy = svy - uy;
+        const int late = (c >= s.I(S::FL + e)) ? 0 : 2;
+        px = fm(wx, k, fm(ux, tj, spx)) + s.F(S::OFF + 4 * e + late);
+        py = fm(wy, k, fm(uy, tj, spy)) + s.F(S::OFF + 4 * e + late + 1);
+        vx = fm(wx, g, ux);
+        vy = fm(wy, g, uy);
+    }
+
+    // start a new segment of body e at column c with state (px,py,vx,vy); prev = state at c-1
+    RGS_DEV void start_segment(int e, int c, T px, T py, T vx, T vy, T qx, T qy, T qvx, T qvy) const {
+        s.F(S::PRV + 4 * e) = qx; s.F(S::PRV + 4 * e + 1) = qy; s.F(S::PRV + 4 * e + 2) = qvx; s.F(S::PRV + 4 * e + 3) = qvy;
+        s.F(S::SP + 4 * e) = px; s.F(S::SP + 4 * e + 1) = py; s.F(S::SP + 4 * e + 2) = vx; s.F(S::SP + 4 * e + 3) = vy;
+        s.F(S::OFF + 4 * e) = T(0); s.F(S::OFF + 4 * e + 1) = T(0); s.F(S::OFF + 4 * e + 2) = T(0); s.F(S::OFF + 4 * e + 3) = T(0);
+        s.I(S::CS + e) = c;
+        s.I(S::FL + e) = c;
+    }
+
+    // bounding interval of body e over columns CS[e]..50 (monotone-velocity bound + offsets)
+    RGS_DEV void update_bbox(int e) const {
+        const int ty = (e == PK);
+        const int cs = s.I(S::CS + e);
+        const int rem = kGrid - cs;
+        const T trem = P.d.dt_col * T(rem), gE = tab->g[ty][rem];
+#pragma unroll
+        for (int a = 0; a < 2; ++a) {
+            const T p = s.F(S::SP + 4 * e + a), v = s.F(S::SP + 4 * e + 2 + a), u = s.F(S::CMD + 2 * e + a);
+            const T vE = fm(v - u, gE, u);
+            const T o1 = s.F(S::OFF + 4 * e + a), o2 = s.F(S::OFF + 4 * e + 2 + a);
+            const T lo = p + tmin(T(0), tmin(v, vE) * trem) + tmin(T(0), tmin(o1, o2));
+            const T hi = p + tmax(T(0), tmax(v, vE) * trem) + tmax(T(0), tmax(o1, o2));
+            s.F(S::BB + 4 * e + 2 * a) = lo;
+            s.F(S::BB + 4 * e + 2 * a + 1) = hi;
+        }
+    }
+
+    static RGS_DEV int pair_index(int a, int b) {  // a < b
+        return a * (2 * E - a - 1) / 2 + (b - a - 1);
+    }
+    static RGS_DEV void pair_decode(int idx, int &a, int &b) {
+        a = 0;
+#pragma unroll 1
+        while (idx >= E - 1 - a) { idx -= E - 1 - a; ++a; }
+        b = a + 1 + idx;
+    }
+
+    // broad-phase flags of body e against the four walls (bits 4e + wall)
+    RGS_DEV void flag_walls(int e, Bits<4 * E> &wb) const {
+        const int ty = (e == PK);
+        const T sl = Slack<T>::v;
+        const T lx = P.lim_x[ty] - sl, ly = P.lim_y[ty] - sl;
+        if (s.F(S::BB + 4 * e + 3) >= ly) wb.set(4 * e + WALL_UP);
+        if (s.F(S::BB + 4 * e + 2) <= -ly) wb.set(4 * e + WALL_DOWN);
+        if (s.F(S::BB + 4 * e + 1) >= lx) wb.set(4 * e + WALL_RIGHT);
+        if (s.F(S::BB + 4 * e + 0) <= -lx) wb.set(4 * e + WALL_LEFT);
+    }
+    // can the bounding intervals of a and b come within r_a + r_b of each other?
+    RGS_DEV bool flag_pair(int a, int b) const {
+        const T gx = tmax(T(0), tmax(s.F(S::BB + 4 * a) - s.F(S::BB + 4 * b + 1), s.F(S::BB + 4 * b) - s.F(S::BB + 4 * a + 1)));
+        const T gy = tmax(T(0), tmax(s.F(S::BB + 4 * a + 2) - s.F(S::BB + 4 * b + 3), s.F(S::BB + 4 * b + 2) - s.F(S::BB + 4 * a + 3)));
+        const T sg = P.d.sig[a == PK][b == PK] + Slack<T>::v;
+        return fm(gx, gx, gy * gy) <= sg * sg;
+    }
+
+    // ---- narrow phase: one item marched over the columns (insertCollisions :362-507, one test) ----
+    // first column c >= base at which body a overlaps wall wk AND the back-tracked time of impact
+    // is valid (approaching at column c-1, inside this step); kGrid+1 when there is none
+    RGS_DEV int search_wall(int a, int wk, int base, T &t_out) const {
+        const int ty = (a == PK);
+        const bool xa = wk >= 2;
+        const T sgn = (wk == WALL_UP || wk == WALL_RIGHT) ? T(1) : T(-1);
+        const T lim = xa ? P.lim_x[ty] : P.lim_y[ty];
+        T px, py, vx, vy;
+        eval(a, base - 1, px, py, vx, vy);
+        T pm = sgn * (xa ? px : py), vm = sgn * (xa ? vx : vy);
+        eval(a, base, px, py, vx, vy);
+        T p = sgn * (xa ? px : py);
+        const T u = sgn * s.F(S::CMD + 2 * a + (xa ? 0 : 1));
+        T w = sgn * (xa ? vx : vy) - u;
+        const T R = tab->g[ty][1], k1 = tab->k[ty][1], uh = u * P.d.dt_col;
+        const int fl = s.I(S::FL + a);
+        const T doff = sgn * (s.F(S::OFF + 4 * a + (xa ? 0 : 1)) - s.F(S::OFF + 4 * a + (xa ? 2 : 3)));
+#pragma unroll 1
+        for (int c = base; c <= kGrid; ++c) {
+            if (p >= lim && vm > T(0)) {
+                const T tc = P.d.dt_col * T(c - 1) + tmax(T(0), (lim - pm) / vm);
+                if (tc < P.d.dt) { t_out = tc; return c; }
+            }
+            pm = p;
+            vm = u + w;
+            p = fm(w, k1, p + uh);
+            w = w * R;
+            if (c + 1 == fl) p += doff;
+        }
+        return kGrid + 1;
+    }
+
+    // same for the pair (a, b); the time is symmetric in (a, b) as in the reference (:482-494)
+    RGS_DEV int search_pair(int a, int b, int base, T &t_out) const {
+        const int tya = (a == PK), tyb = (b == PK);
+        const T thr = P.d.ov_le[tya][tyb], sigma = P.d.sig[tya][tyb];
+        T amx, amy, amvx, amvy, bmx, bmy, bmvx, bmvy, ax, ay, avx, avy, bx, by, bvx, bvy;
+        eval(a, base - 1, amx, amy, amvx, amvy);
+        eval(b, base - 1, bmx, bmy, bmvx, bmvy);
+        eval(a, base, ax, ay, avx, avy);
+        eval(b, base, bx, by, bvx, bvy);
+        const T uax = s.F(S::CMD + 2 * a), uay = s.F(S::CMD + 2 * a + 1), ubx = s.F(S::CMD + 2 * b), uby = s.F(S::CMD + 2 * b + 1);
+        T wax = avx - uax, way = avy - uay, wbx = bvx - ubx, wby = bvy - uby;
+        const T h = P.d.dt_col;
+        const T Ra = tab->g[tya][1], ka = tab->k[tya][1], Rb = tab->g[tyb][1], kb = tab->k[tyb][1];
+        const T uaxh = uax * h, uayh = uay * h, ubxh = ubx * h, ubyh = uby * h;
+        const int fla = s.I(S::FL + a), flb = s.I(S::FL + b);
+        const T dax = s.F(S::OFF + 4 * a) - s.F(S::OFF + 4 * a + 2), day = s.F(S::OFF + 4 * a + 1) - s.F(S::OFF + 4 * a + 3);
+        const T dbx = s.F(S::OFF + 4 * b) - s.F(S::OFF + 4 * b + 2), dby = s.F(S::OFF + 4 * b + 1) - s.F(S::OFF + 4 * b + 3);
+#pragma unroll 1
+        for (int c = base; c <= kGrid; ++c) {
+            const T ex = ax - bx, ey = ay - by;
+            if (fm(ex, ex, ey * ey) <= thr) {
+                const T dpx = bmx - amx, dpy = bmy - amy, dvx = bmvx - amvx, dvy = bmvy - amvy;
+                const T dpdv = fm(dpx, dvx, dpy * dvy), dvdv = fm(dvx, dvx, dvy * dvy), dpdp = fm(dpx, dpx, dpy * dpy);
+                const T d = dpdv * dpdv - dvdv * (dpdp - sigma * sigma);
+                if (dpdv < T(0) && d >= T(0)) {
+                    const T tc = h * T(c - 1) + tmax(T(0), -(dpdv + T(sqrt(d))) / dvdv);
+                    if (tc < P.d.dt) { t_out = tc; return c; }
+                }
+            }
+            amx = ax; amy = ay; amvx = uax + wax; amvy = uay + way;
+            bmx = bx; bmy = by; bmvx = ubx + wbx; bmvy = uby + wby;
+            ax = fm(wax, ka, ax + uaxh); ay = fm(way, ka, ay + uayh);
+            bx = fm(wbx, kb, bx + ubxh); by = fm(wby, kb, by + ubyh);
+            wax *= Ra; way *= Ra; wbx *= Rb; wby *= Rb;
+            if (c + 1 == fla) { ax += dax; ay += day; }
+            if (c + 1 == flb) { bx += dbx; by += dby; }
+        }
+        return kGrid + 1;
+    }
+
+    // candidate (c, t, kind, j) of owner e: keep it if it beats the owner's current candidate in the
+    // reference's order: earlier column; same column: smaller t; same t: earlier in the candidate
+    // order walls UP, DOWN, RIGHT, LEFT, bodies in entity order (strict '<', :389,:412,:435,:458,:495)
+    RGS_DEV void fold(int e, int c, T t, int kind, int j, unsigned &fmask) const {
+        const int rank = kind < PAIR ? kind : PAIR + j;
+        bool better = true;
+        if ((fmask >> e) & 1u) {
+            const int qi = s.I(S::QI + e);
+            const int bc = (qi >> 8) & 63, bk = (qi >> 4) & 15, bj = qi & 15;
+            const int brank = bk < PAIR ? bk : PAIR + bj;
+            const T bt = s.F(S::QT + e);
+            better = c < bc || (c == bc && (t < bt || (t == bt && rank < brank)));
+        }
+        if (better) {
+            s.F(S::QT + e) = t;
+            s.I(S::QI + e) = (c << 8) | (kind << 4) | (j & 15);
+            fmask |= 1u << e;
+        }
+    }
+
+    RGS_DEV void run_items(Bits<4 * E> &wb, Bits<NPAIR> &pb, unsigned owners, int base, unsigned &fmask) const {
+        int bit;
+#pragma unroll 1
+        while ((bit = wb.pop()) >= 0) {
+            const int a = bit >> 2, wk = bit & 3;
+            T t;
+            const int c = search_wall(a, wk, base, t);
+            if (c <= kGrid) fold(a, c, t, wk, 15, fmask);
+        }
+#pragma unroll 1
+        while ((bit = pb.pop()) >= 0) {
+            int a, b;
+            pair_decode(bit, a, b);
+            T t;
+            const int c = search_pair(a, b, base, t);
+            if (c <= kGrid) {
+                if ((owners >> a) & 1u) fold(a, c, t, PAIR, b, fmask);
+                if ((owners >> b) & 1u) fold(b, c, t, PAIR, a, fmask);
+            }
+        }
+    }
+
+    // ---- event queue: <= one event per owner body (reference src/GameSim.cpp:136-150) ----
+    // QI = (seq << 16) | (col << 8) | (kind << 4) | j  (j = 15 for walls)
+    RGS_DEV void push(int e, unsigned &qmask, int &seq) const {
+        s.I(S::QI + e) = (s.I(S::QI + e) & 0xFFFF) | (seq << 16);
+        qmask |= 1u << e;
+        ++seq;
+    }
+    // earliest time; among equal times the most recently inserted (stable insertion sort, a11)
+    RGS_DEV void pop(unsigned &qmask, int &ei, int &ej, int &ekind, T &et) const {
+        int best = -1, binfo = 0;
+        T bt = T(0);
+#pragma unroll 1
+        for (int e = 0; e < E; ++e) {
+            if ((qmask >> e) & 1u) {
+                const T te = s.F(S::QT + e);
+                const int info = s.I(S::QI + e);
+                if (best < 0 || te < bt || (te == bt && (info >> 16) > (binfo >> 16))) { best = e; bt = te; binfo = info; }
+            }
+        }
+        ei = best;
+        et = bt;
+        ekind = (binfo >> 4) & 15;
+        ej = binfo & 15;
+        if (ej == 15) ej = -1;
+        qmask &= ~(1u << best);
+    }
+    // drop queued events sharing a body with the executed one (:347-352)
+    RGS_DEV void prune(unsigned &qmask, int ei, int ej) const {
+#pragma unroll 1
+        for (int e = 0; e < E; ++e) {
+            if ((qmask >> e) & 1u) {
+                int cj = s.I(S::QI + e) & 15;
+                if (cj == 15) cj = -1;
+                const bool drop = (ei == e) || (ei == cj && cj != -1) || (ej == e) || (ej == cj && cj != -1);
+                if (drop) qmask &= ~(1u << e);
+            }
+        }
+    }
+
+    // correctOverlap on the columns after an impact (:285-297): march the pair from its new
+    // segments, record the position offsets
+    RGS_DEV void march_pair(int bi, int bj, int base, long long *ev) const {
+        const int tyi = (bi == PK), tyj = (bj == PK);
+        T ax = s.F(S::SP + 4 * bi), ay = s.F(S::SP + 4 * bi + 1), bx = s.F(S::SP + 4 * bj), by = s.F(S::SP + 4 * bj + 1);
+        const T uax = s.F(S::CMD + 2 * bi), uay = s.F(S::CMD + 2 * bi + 1), ubx = s.F(S::CMD + 2 * bj), uby = s.F(S::CMD + 2 * bj + 1);
+        T wax = s.F(S::SP + 4 * bi + 2) - uax, way = s.F(S::SP + 4 * bi + 3) - uay;
+        T wbx = s.F(S::SP + 4 * bj + 2) - ubx, wby = s.F(S::SP + 4 * bj + 3) - uby;
+        const T h = P.d.dt_col;
+        const T Ra = tab->g[tyi][1], ka = tab->k[tyi][1], Rb = tab->g[tyj][1], kb = tab->k[tyj][1];
+        const T uaxh = uax * h, uayh = uay * h, ubxh = ubx * h, ubyh = uby * h;
+        const T thr = P.d.ov_lt[tyi][tyj];
+#pragma unroll 1
+        for (int c = base + 1; c <= kGrid; ++c) {
+            ax = fm(wax, ka, ax + uaxh); ay = fm(way, ka, ay + uayh);
+            bx = fm(wbx, kb, bx + ubxh); by = fm(wby, kb, by + ubyh);
+            wax *= Ra; way *= Ra; wbx *= Rb; wby *= Rb;
+            const T dx = bx - ax, dy = by - ay;
+            const T ssq = fm(dx, dx, dy * dy);
+            if (ssq <= thr) {
+                const T overlap = P.d.sig[tyi][tyj] - T(sqrt(ssq));
+                const T si = P.d.fix_coef[tyi][tyj] * overlap, sj = P.d.fix_coef[tyj][tyi] * overlap;
+                const T fax = -(si * dx), fay = -(si * dy), fbx = sj * dx, fby = sj * dy;
+                ax += fax; ay += fay; bx += fbx; by += fby;
+                s.F(S::OFF + 4 * bi + 2) = s.F(S::OFF + 4 * bi); s.F(S::OFF + 4 * bi + 3) = s.F(S::OFF + 4 * bi + 1);
+                s.F(S::OFF + 4 * bi) += fax; s.F(S::OFF + 4 * bi + 1) += fay;
+                s.F(S::OFF + 4 * bj + 2) = s.F(S::OFF + 4 * bj); s.F(S::OFF + 4 * bj + 3) = s.F(S::OFF + 4 * bj + 1);
+                s.F(S::OFF + 4 * bj) += fbx; s.F(S::OFF + 4 * bj + 1) += fby;
+                s.I(S::FL + bi) = c;
+                s.I(S::FL + bj) = c;
+                ev[RGS_EV_OVERLAP_FIXES]++;
+            }
+        }
+    }
+    // same for a body and the wall it hit (:329-340)
+    RGS_DEV void march_wall(int bi, int wk, int base, long long *ev) const {
+        const int ty = (bi == PK);
+        const int ax = wk >= 2 ? 0 : 1;
+        const T sgn = (wk == WALL_UP || wk == WALL_RIGHT) ? T(1) : T(-1);
+        const T lim = ax == 0 ? P.lim_x[ty] : P.lim_y[ty];
+        const T lim_in = ax == 0 ? P.lim_x_in[ty] : P.lim_y_in[ty];
+        const T u = sgn * s.F(S::CMD + 2 * bi + ax);
+        T p = sgn * s.F(S::SP + 4 * bi + ax);
+        T w = sgn * s.F(S::SP + 4 * bi + 2 + ax) - u;
+        const T R = tab->g[ty][1], k1 = tab->k[ty][1], uh = u * P.d.dt_col;
+#pragma unroll 1
+        for (int c = base + 1; c <= kGrid; ++c) {
+            p = fm(w, k1, p + uh);
+            w *= R;
+            if (p >= lim) {  // correctOverlap(wall) :594-623, kept strictly inside the limit
+                const T pc = tmin(p - P.d.wall_fix * (p - lim), lim_in);
+                const T f = pc - p;
+                p = pc;
+                s.F(S::OFF + 4 * bi + 2 + ax) = s.F(S::OFF + 4 * bi + ax);
+                s.F(S::OFF + 4 * bi + 2 + (1 - ax)) = s.F(S::OFF + 4 * bi + (1 - ax));
+                s.F(S::OFF + 4 * bi + ax) += sgn * f;
+                s.I(S::FL + bi) = c;
+                ev[RGS_EV_OVERLAP_FIXES]++;
+            }
+        }
+    }
+
+    // ---- one game-step (GameSim::updateSim :126-171); SP/CMD hold the state and the commands ----
+    // returns the event-loop counter of the step (1 when nothing happened)
+    RGS_DEV int step(double &sa, double &sb, long long *ev, double *dmg, long long live) const {
+        Bits<4 * E> wb;
+        Bits<NPAIR> pb;
+        wb.clear();
+        pb.clear();
+#pragma unroll 1
+        for (int e = 0; e < E; ++e) {
+            s.I(S::CS + e) = 0;
+            s.I(S::FL + e) = 0;
+            s.F(S::OFF + 4 * e) = T(0); s.F(S::OFF + 4 * e + 1) = T(0); s.F(S::OFF + 4 * e + 2) = T(0); s.F(S::OFF + 4 * e + 3) = T(0);
+            update_bbox(e);
+            flag_walls(e, wb);
+        }
+#pragma unroll 1
+        for (int a = 0; a < E - 1; ++a)
+#pragma unroll 1
+            for (int b = a + 1; b < E; ++b)
+                if (flag_pair(a, b)) pb.set(pair_index(a, b));
+        int counter = 1;
+        if (wb.any() || pb.any()) {
+            unsigned qmask = 0, fmask = 0, owners = (1u << E) - 1u;
+            int seq = 0, base = 1, ri = -1, rj = -1;
+            bool scored = false;
+#pragma unroll 1
+            for (;;) {
+                fmask = 0;
+                run_items(wb, pb, owners, base, fmask);
+                if (ri < 0) {
+#pragma unroll 1
+                    for (int e = 0; e < E; ++e)
+                        if ((fmask >> e) & 1u) push(e, qmask, seq);
+                } else {
+                    if ((fmask >> ri) & 1u) push(ri, qmask, seq);
+                    if (rj >= 0 && ((fmask >> rj) & 1u)) push(rj, qmask, seq);
+                }
+                if (qmask == 0 || counter >= kCounterLim) break;
+                int ei, ej, ekind;
+                T et;
+                pop(qmask, ei, ej, ekind, et);
+                ri = ei; rj = -1; owners = 0;  // nothing to re-scan unless the event executes
+                if ((ei == PK || ej == PK) && scored) {  // :230-231
+                    ev[RGS_EV_DISCARDED]++;
+                    hash_event(ev, live, DISCARD, ei, ej, 0);
+                    ++counter;
+                    continue;
+                }
+                {
+                    int nb = (int)floor(et / P.d.dt_col) + 1;  // :237
+                    if (nb > kGrid) { nb = kGrid; ev[RGS_EV_BASE_CLAMP]++; }
+                    if (nb > base) base = nb;  // event times never run backwards by more than a rounding
+                }
+                const T dt_t = et - P.d.dt_col * T(base - 1);  // :254 / :308
+                const T h_rest = P.d.dt_col - dt_t;
+                int goal = 0;
+                const int tyi = (ei == PK);
+                T qix, qiy, qvix, qviy;
+                eval(ei, base - 1, qix, qiy, qvix, qviy);
+                T pix = qix, piy = qiy, vix = qvix, viy = qviy;
+                const T uix = s.F(S::CMD + 2 * ei), uiy = s.F(S::CMD + 2 * ei + 1);
+                advance_axis(pix, vix, uix, dt_t, P.neg_inv_tau[tyi]);
+                advance_axis(piy, viy, uiy, dt_t, P.neg_inv_tau[tyi]);
+                if (ekind == PAIR) {  // :242-299
+                    const int tyj = (ej == PK);
+                    T qjx, qjy, qvjx, qvjy;
+                    eval(ej, base - 1, qjx, qjy, qvjx, qvjy);
+                    T pjx = qjx, pjy = qjy, vjx = qvjx, vjy = qvjy;
+                    const T ujx = s.F(S::CMD + 2 * ej), ujy = s.F(S::CMD + 2 * ej + 1);
+                    advance_axis(pjx, vjx, ujx, dt_t, P.neg_inv_tau[tyj]);
+                    advance_axis(pjy, vjy, ujy, dt_t, P.neg_inv_tau[tyj]);
+                    {  // residual overlap of the constant-velocity impact-time estimate :259-265
+                        const T dx = pjx - pix, dy = pjy - piy;
+                        const T ssq = dx * dx + dy * dy;
+                        if (ssq <= P.d.ov_lt[tyi][tyj]) {
+                            const T overlap = P.d.sig[tyi][tyj] - T(sqrt(ssq));
+                            const T si = P.d.hit_coef[tyi][tyj] * overlap, sj = P.d.hit_coef[tyj][tyi] * overlap;
+                            pix -= si * dx; piy -= si * dy;
+                            pjx += sj * dx; pjy += sj * dy;
+                        }
+                    }
+                    {  // elastic impulse :268-274
+                        const T dvx = vix - vjx, dvy = viy - vjy, dpx = pix - pjx, dpy = piy - pjy;
+                        const T dot = fm(dvx, dpx, dvy * dpy), nn = fm(dpx, dpx, dpy * dpy);
+                        const T fi = P.d.imp_coef[tyi][tyj] * dot / nn, fj = P.d.imp_coef[tyj][tyi] * dot / nn;
+                        if (ei != PK && ej != PK) {  // damage :277-282
+                            const double dv_sq = 0.01 * ((double)dvx * (double)dvx + (double)dvy * (double)dvy);
+                            dmg[ei * NP + ej] += (double)P.d.mass[tyi] * dv_sq;
+                            dmg[ej * NP + ei] += (double)P.d.mass[tyj] * dv_sq;
+                            ev[RGS_EV_PLAYER_PLAYER]++;
+                        } else {
+                            ev[RGS_EV_PLAYER_PUCK]++;
+                        }
+                        vix -= fi * dpx; viy -= fi * dpy;
+                        vjx += fj * dpx; vjy += fj * dpy;
+                    }
+                    advance_axis(pix, vix, uix, h_rest, P.neg_inv_tau[tyi]);
+                    advance_axis(piy, viy, uiy, h_rest, P.neg_inv_tau[tyi]);
+                    advance_axis(pjx, vjx, ujx, h_rest, P.neg_inv_tau[tyj]);
+                    advance_axis(pjy, vjy, ujy, h_rest, P.neg_inv_tau[tyj]);
+                    {  // correctOverlap at column base :287
+                        const T dx = pjx - pix, dy = pjy - piy;
+                        const T ssq = dx * dx + dy * dy;
+                        if (ssq <= P.d.ov_lt[tyi][tyj]) {
+                            const T overlap = P.d.sig[tyi][tyj] - T(sqrt(ssq));
+                            const T si = P.d.fix_coef[tyi][tyj] * overlap, sj = P.d.fix_coef[tyj][tyi] * overlap;
+                            pix -= si * dx; piy -= si * dy;
+                            pjx += sj * dx; pjy += sj * dy;
+                            ev[RGS_EV_OVERLAP_FIXES]++;
+                        }
+                    }
+                    start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
+                    start_segment(ej, base, pjx, pjy, vjx, vjy, qjx, qjy, qvjx, qvjy);
+                    march_pair(ei, ej, base, ev);
+                    update_bbox(ej);
+                    rj = ej;
+                } else {  // wall :300-343
+                    switch (ekind) {  // flip only while still moving into the wall :312-318
+                    case WALL_UP: if (viy > T(0)) viy = -viy; break;
+                    case WALL_DOWN: if (viy < T(0)) viy = -viy; break;
+                    case WALL_RIGHT: if (vix > T(0)) vix = -vix; break;
+                    default: if (vix < T(0)) vix = -vix; break;
+                    }
+                    const bool is_goal = (ei == PK) && (ekind == WALL_LEFT || ekind == WALL_RIGHT) && piy < P.d.half_goal &&
+                                         piy > -P.d.half_goal;  // :321-322
+                    if (is_goal) {
+                        if (ekind == WALL_RIGHT) { sa += 1.0; goal = 1; } else { sb += 1.0; goal = 2; }
+                        ev[goal == 1 ? RGS_EV_GOALS_A : RGS_EV_GOALS_B]++;
+                        scored = true;
+                        pix = piy = vix = viy = T(0);  // puck reset :325
+                    } else {
+                        advance_axis(pix, vix, uix, h_rest, P.neg_inv_tau[tyi]);
+                        advance_axis(piy, viy, uiy, h_rest, P.neg_inv_tau[tyi]);
+                        {  // correctOverlap(wall) at column base :334 (folded limit, kept strictly inside)
+                            const bool xa = ekind >= WALL_RIGHT;
+                            const T sgn = (ekind == WALL_UP || ekind == WALL_RIGHT) ? T(1) : T(-1);
+                            const T lim = xa ? P.lim_x[tyi] : P.lim_y[tyi], lim_in = xa ? P.lim_x_in[tyi] : P.lim_y_in[tyi];
+                            const T q = sgn * (xa ? pix : piy);
+                            if (q >= lim) {
+                                const T qc = sgn * tmin(q - P.d.wall_fix * (q - lim), lim_in);
+                                if (xa) pix = qc; else piy = qc;
+                                ev[RGS_EV_OVERLAP_FIXES]++;
+                            }
+                        }
+                    }
+                    ev[RGS_EV_WALL_UP + ekind]++;
+                    start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
+                    if (!is_goal) march_wall(ei, ekind, base, ev);
+                }
+                update_bbox(ei);
+                hash_event(ev, live, ekind, ei, ej, goal);
+                prune(qmask, ei, ej);  // :347-352
+                // re-scan the bodies involved (:355-357, :147): broad phase on their new segments
+                owners = 1u << ei;
+                flag_walls(ei, wb);
+                if (rj >= 0) {
+                    owners |= 1u << rj;
+                    flag_walls(rj, wb);
+                }
+#pragma unroll 1
+                for (int o = 0; o < E; ++o) {
+                    if (o != ei && flag_pair(ei, o)) pb.set(o < ei ? pair_index(o, ei) : pair_index(ei, o));
+                    if (rj >= 0 && o != rj && o != ei && flag_pair(rj, o)) pb.set(o < rj ? pair_index(o, rj) : pair_index(rj, o));
+                }
+                ++counter;
+            }
+            if (qmask != 0) ev[RGS_EV_COUNTER_LIMIT]++;
+        }
+        // commit column 50 (:153-157)
+#pragma unroll 1
+        for (int e = 0; e < E; ++e) {
+            T px, py, vx, vy;
+            eval(e, kGrid, px, py, vx, vy);
+            s.F(S::SP + 4 * e) = px; s.F(S::SP + 4 * e + 1) = py; s.F(S::SP + 4 * e + 2) = vx; s.F(S::SP + 4 * e + 3) = vy;
+        }
+        return counter;
+    }
+};
+
+// trajectory record [t, state (reference order), damage] after step k
+template <typename T, int NT>
+RGS_DEV void write_traj_lane(const RunArgs &A, const LaneScratch<T, NT> &s, int64_t game, int64_t k, double t_clock, double sa,
+                             double sb) {
+    constexpr int E = 2 * NT + 1, PK = 2 * NT, SREC = 2 + 4 * E, NP = 2 * NT, TREC = 1 + SREC + NP * NP;
+    using S = LaneScratch<T, NT>;
+    double *rec = A.traj + (game * (A.n_steps / A.log_stride) + ((k + 1) / A.log_stride - 1)) * TREC;
+    rec[0] = t_clock;
+    rec[1] = sa;
+    rec[2] = sb;
+#pragma unroll 1
+    for (int slot = 0; slot < E; ++slot) {
+        const int e = slot == 0 ? PK : slot - 1;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) rec[3 + 4 * slot + c] = (double)s.F(S::SP + 4 * e + c);
+    }
+#pragma unroll 1
+    for (int d = 0; d < NP * NP; ++d) rec[1 + SREC + d] = A.damage[game * (NP * NP) + d];
+}
+
+// all n_steps of ONE game (the body of a lane)
+template <typename T, int NT>
+RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const LaneTab<T> *tab, const LaneScratch<T, NT> &s,
+                               int64_t game) {
+    constexpr int E = 2 * NT + 1, PK = 2 * NT, SREC = 2 + 4 * E, NP = 2 * NT;
+    using S = LaneScratch<T, NT>;
+    const LaneGame<T, NT> G(P, tab, s);
+    double *srec = A.state + game * SREC;
+#pragma unroll 1
+    for (int slot = 0; slot < E; ++slot) {
+        const int e = slot == 0 ? PK : slot - 1;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const T v = T(srec[2 + 4 * slot + c]);
+            s.F(S::SP + 4 * e + c) = v;
+            s.F(S::PRV + 4 * e + c) = v;
+        }
+        s.F(S::CMD + 2 * e) = T(0);
+        s.F(S::CMD + 2 * e + 1) = T(0);
+    }
+    double sa = srec[0], sb = srec[1];
+    double t_clock = A.clock[game];
+    long long *gev = A.events + game * RGS_N_EVENTS;
+    double *dmg = A.damage + game * (NP * NP);
+    long long live = gev[RGS_EV_LIVE_STEPS], loop_iters = gev[RGS_EV_LOOP_ITERS], decided = gev[RGS_EV_DECIDED_STEP];
+    const T *actions = static_cast<const T *>(A.actions);
+    const double wsc = (double)P.d.winning_score;
+    // command record index without a division per step
+    int64_t aidx = A.synth ? A.step0 / A.hold : 0;
+    int64_t phase = A.synth ? A.step0 % A.hold : 0;
+    bool fetch = true;
+    const bool logging = A.traj != nullptr && A.log_stride > 0;
+    int64_t k = 0, log_left = A.log_stride;
+#pragma unroll 1
+    for (; k < A.n_steps; ++k) {
+        if (!(sa < wsc && sb < wsc)) break;  // undecided(), :57-60
+        if (fetch) {
+            const int64_t ai = (A.synth || aidx < A.n_act) ? aidx : A.n_act - 1;
+#pragma unroll 1
+            for (int c = 0; c < 2 * NP; ++c)
+                s.F(S::CMD + c) = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
+                                          : actions[game * A.act_game_stride + ai * (2 * NP) + c];
+            fetch = false;
+        }
+        if (++phase == A.hold) { phase = 0; ++aidx; fetch = true; }
+        loop_iters += G.step(sa, sb, gev, dmg, live);
+        t_clock += (double)P.d.dt;  // t_ += dt_ (:158), fp64 like the reference clock
+        ++live;
+        if (decided == 0 && !(sa < wsc && sb < wsc)) decided = live;
+        if (logging && --log_left == 0) {
+            log_left = A.log_stride;
+            write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb);
+        }
+    }
+    if (logging)  // frozen steps of a decided game (GameSim::run :121-123) repeat the frozen state
+        for (; k < A.n_steps; ++k)
+            if (--log_left == 0) { log_left = A.log_stride; write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb); }
+    srec[0] = sa;
+    srec[1] = sb;
+#pragma unroll 1
+    for (int slot = 0; slot < E; ++slot) {
+        const int e = slot == 0 ? PK : slot - 1;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) srec[2 + 4 * slot + c] = (double)s.F(S::SP + 4 * e + c);
+    }
+    A.clock[game] = t_clock;
+    gev[RGS_EV_LIVE_STEPS] = live;
+    gev[RGS_EV_LOOP_ITERS] = loop_iters;
+    gev[RGS_EV_DECIDED_STEP] = decided;
+}
+
+}  // namespace rgs

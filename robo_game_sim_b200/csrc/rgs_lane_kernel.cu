@@ -1,0 +1,76 @@
+// rgs_lane_kernel.cu -- K2 launch wrapper: fused multi-step rollout, throughput formulation, one
+// LANE per game (see rgs_lane.cuh).  fp32 = throughput mode, fp64 = validation of the formulation.
+//
+// Shared memory per CTA: the closed-form coefficient table + one scratch record per thread, laid
+// out word-major ([word][thread]) so that the run-time body indices of the event path never cause
+// a bank conflict (bank = lane) and never force per-thread arrays into local memory.
+#include "rgs_lane.cuh"
+#include "rgs_host_params.h"
+#include "rgs_kernels.h"
+
+namespace rgs {
+
+template <typename T, int NT, int THREADS>
+__global__ void __launch_bounds__(THREADS) rollout_lane_kernel(const __grid_constant__ FastParams<T> P,
+                                                               const __grid_constant__ RunArgs A) {
+    using S = LaneScratch<T, NT>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    LaneTab<T> *tab = reinterpret_cast<LaneTab<T> *>(smem_raw);
+    constexpr size_t tab_bytes = (sizeof(LaneTab<T>) + 15) & ~size_t(15);
+    T *fw = reinterpret_cast<T *>(smem_raw + tab_bytes);
+    int *iw = reinterpret_cast<int *>(fw + (size_t)S::NF * THREADS);
+    for (int i = threadIdx.x; i < 2 * kCols; i += THREADS) {
+        (&tab->g[0][0])[i] = (&P.tab_g[0][0])[i];
+        (&tab->k[0][0])[i] = (&P.tab_k[0][0])[i];
+    }
+    __syncthreads();
+    const S s{fw + threadIdx.x, iw + threadIdx.x, THREADS};
+    const int64_t stride = (int64_t)gridDim.x * THREADS;
+    for (int64_t game = (int64_t)blockIdx.x * THREADS + threadIdx.x; game < A.n_games; game += stride)
+        rollout_lane_game<T, NT>(P, A, tab, s, game);
+}
+
+template <typename T, int NT>
+static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count) {
+    using S = LaneScratch<T, NT>;
+    constexpr int kThreads = 64;
+    constexpr size_t tab_bytes = (sizeof(LaneTab<T>) + 15) & ~size_t(15);
+    const size_t smem = tab_bytes + ((size_t)S::NF * sizeof(T) + (size_t)S::NI * sizeof(int)) * kThreads;
+    auto kern = rollout_lane_kernel<T, NT, kThreads>;
+    cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    int per_sm = 0;
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem);
+    if (err != cudaSuccess) return err;
+    if (per_sm < 1) per_sm = 1;
+    int64_t blocks = (A.n_games + kThreads - 1) / kThreads;
+    const int64_t cap = (int64_t)sm_count * per_sm;  // persistent grid: resident CTAs x SM count
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    kern<<<(unsigned)blocks, kThreads, smem, stream>>>(P, A);
+    return cudaGetLastError();
+}
+
+template <typename T>
+static cudaError_t launch_lane(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count) {
+    const FastParams<T> P = make_fast_params<T>(p);
+    switch (n_team) {
+    case 1: return launch_lane_nt<T, 1>(P, A, stream, sm_count);
+    case 2: return launch_lane_nt<T, 2>(P, A, stream, sm_count);
+    case 3: return launch_lane_nt<T, 3>(P, A, stream, sm_count);
+    case 4: return launch_lane_nt<T, 4>(P, A, stream, sm_count);
+    case 5: return launch_lane_nt<T, 5>(P, A, stream, sm_count);
+    case 6: return launch_lane_nt<T, 6>(P, A, stream, sm_count);
+    case 7: return launch_lane_nt<T, 7>(P, A, stream, sm_count);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+cudaError_t launch_rollout_lane_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count) {
+    return launch_lane<float>(n_team, p, A, stream, sm_count);
+}
+cudaError_t launch_rollout_lane_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count) {
+    return launch_lane<double>(n_team, p, A, stream, sm_count);
+}
+
+}  // namespace rgs

@@ -8,6 +8,7 @@
 //
 #include "../../robo_game_sim_b200/csrc/rgs_exact.cuh"
 #include "../../robo_game_sim_b200/csrc/rgs_fast.cuh"
+#include "../../robo_game_sim_b200/csrc/rgs_lane.cuh"
 #include "../../robo_game_sim_b200/csrc/rgs_host_params.h"
 
 #include <memory>
@@ -31,11 +32,30 @@ void run_fast(const rgs_params &p, const rgs::RunArgs &A) {
     emu::run_warp([&](int lane) { rgs::rollout_fast_warp<T, NT>(P, A, W.get(), tab.get(), lane, 0, 1); });
 }
 
+template <typename T, int NT>
+void run_lane(const rgs_params &p, const rgs::RunArgs &A) {
+    using S = rgs::LaneScratch<T, NT>;
+    auto tab = std::make_unique<rgs::LaneTab<T>>();
+    const rgs::FastParams<T> P = rgs::make_fast_params<T>(p);
+    for (int ty = 0; ty < 2; ++ty)
+        for (int i = 0; i < rgs::kCols; ++i) { tab->g[ty][i] = P.tab_g[ty][i]; tab->k[ty][i] = P.tab_k[ty][i]; }
+    T fw[S::NF];
+    int iw[S::NI];
+    S s{fw, iw, 1};
+    for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT>(P, A, tab.get(), s, g);
+}
+
 template <int NT>
 void dispatch(const rgs_params &p, const rgs::RunArgs &A) {
+    // the FAST modes run the lane body, as librgs_b200.so does; RGS_K2_WARP=1 selects the superseded
+    // warp-per-game body there and here (33 / 66 always mean the lane body: A/B scripts)
+    const char *w = std::getenv("RGS_K2_WARP");
+    const bool warp_k2 = w && w[0] == '1';
     if (p.mode == RGS_MODE_EXACT_F64) run_exact<NT>(p, A);
-    else if (p.mode == RGS_MODE_FAST_F32) run_fast<float, NT>(p, A);
-    else run_fast<double, NT>(p, A);
+    else if (p.mode == RGS_MODE_FAST_F32 && warp_k2) run_fast<float, NT>(p, A);
+    else if (p.mode == RGS_MODE_FAST_F64 && warp_k2) run_fast<double, NT>(p, A);
+    else if (p.mode == RGS_MODE_FAST_F32 || p.mode == 33) run_lane<float, NT>(p, A);
+    else run_lane<double, NT>(p, A);
 }
 
 }  // namespace
