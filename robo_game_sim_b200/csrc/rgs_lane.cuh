@@ -65,11 +65,11 @@ struct LaneScratch {
     RGS_DEV int &I(int w) const { return i[w * stride]; }
 };
 
-struct LaneTabEntry32 { float g, k; };
 template <typename T>
-struct LaneTab {   // block-shared coefficient table, [type][j] -> {R^j, a (1-R^j)/(1-R)}
-    T g[2][kCols];
-    T k[2][kCols];
+struct alignas(2 * sizeof(T)) LaneGK { T g, k; };
+template <typename T>
+struct LaneTab {   // block-shared coefficient table, [type][j] -> {R^j, a (1-R^j)/(1-R)}: one 64/128-bit load
+    LaneGK<T> e[2][kCols];
 };
 
 // small fixed-size bitset in registers
@@ -143,7 +143,8 @@ struct LaneGame {
         if (j == 0) { px = spx; py = spy; vx = svx; vy = svy; return; }
         const int ty = (e == PK);
         const T ux = s.F(S::CMD + 2 * e), uy = s.F(S::CMD + 2 * e + 1);
-        const T g = tab->g[ty][j], k = tab->k[ty][j], tj = P.d.dt_col * T(j);
+        const LaneGK<T> gk = tab->e[ty][j];
+        const T g = gk.g, k = gk.k, tj = P.d.dt_col * T(j);
         const T wx = svx - ux, wy = svy - uy;
         const int late = (c >= s.I(S::FL + e)) ? 0 : 2;
         px = fm(wx, k, fm(ux, tj, spx)) + s.F(S::OFF + 4 * e + late);
@@ -166,7 +167,7 @@ struct LaneGame {
         const int ty = (e == PK);
         const int cs = s.I(S::CS + e);
         const int rem = kGrid - cs;
-        const T trem = P.d.dt_col * T(rem), gE = tab->g[ty][rem];
+        const T trem = P.d.dt_col * T(rem), gE = tab->e[ty][rem].g;
 #pragma unroll
         for (int a = 0; a < 2; ++a) {
             const T p = s.F(S::SP + 4 * e + a), v = s.F(S::SP + 4 * e + 2 + a), u = s.F(S::CMD + 2 * e + a);
@@ -207,75 +208,143 @@ struct LaneGame {
         return fm(gx, gx, gy * gy) <= sg * sg;
     }
 
-    // ---- narrow phase: one item marched over the columns (insertCollisions :362-507, one test) ----
-    // first column c >= base at which body a overlaps wall wk AND the back-tracked time of impact
-    // is valid (approaching at column c-1, inside this step); kGrid+1 when there is none
-    RGS_DEV int search_wall(int a, int wk, int base, T &t_out) const {
-        const int ty = (a == PK);
-        const bool xa = wk >= 2;
+    // ---- narrow phase: one item searched over the columns (insertCollisions :362-507, one test) ----
+    // mirrored single-axis view of body a for wall wk: q = sgn * coordinate, overlap <=> q >= lim
+    struct Axis {
+        T sp, sv, u, w0, off_t, off_b;
+        int cs, fl, ty;
+    };
+    RGS_DEV Axis axis_of(int a, int wk) const {
+        Axis A;
+        const int ax = wk >= 2 ? 0 : 1;
         const T sgn = (wk == WALL_UP || wk == WALL_RIGHT) ? T(1) : T(-1);
-        const T lim = xa ? P.lim_x[ty] : P.lim_y[ty];
-        T px, py, vx, vy;
-        eval(a, base - 1, px, py, vx, vy);
-        T pm = sgn * (xa ? px : py), vm = sgn * (xa ? vx : vy);
-        eval(a, base, px, py, vx, vy);
-        T p = sgn * (xa ? px : py);
-        const T u = sgn * s.F(S::CMD + 2 * a + (xa ? 0 : 1));
-        T w = sgn * (xa ? vx : vy) - u;
-        const T R = tab->g[ty][1], k1 = tab->k[ty][1], uh = u * P.d.dt_col;
-        const int fl = s.I(S::FL + a);
-        const T doff = sgn * (s.F(S::OFF + 4 * a + (xa ? 0 : 1)) - s.F(S::OFF + 4 * a + (xa ? 2 : 3)));
+        A.ty = (a == PK);
+        A.cs = s.I(S::CS + a);
+        A.fl = s.I(S::FL + a);
+        A.sp = sgn * s.F(S::SP + 4 * a + ax);
+        A.sv = sgn * s.F(S::SP + 4 * a + 2 + ax);
+        A.u = sgn * s.F(S::CMD + 2 * a + ax);
+        A.w0 = A.sv - A.u;
+        A.off_t = sgn * s.F(S::OFF + 4 * a + ax);
+        A.off_b = sgn * s.F(S::OFF + 4 * a + 2 + ax);
+        return A;
+    }
+    // q and its velocity at column c >= cs (closed form from the segment start)
+    RGS_DEV void axis_at(const Axis &A, int c, T &q, T &v) const {
+        const int j = c - A.cs;
+        const LaneGK<T> gk = tab->e[A.ty][j];
+        q = fm(A.w0, gk.k, fm(A.u, P.d.dt_col * T(j), A.sp)) + (c >= A.fl ? A.off_t : A.off_b);
+        v = fm(A.w0, gk.g, A.u);
+        if (j == 0) { q = A.sp; v = A.sv; }
+    }
+
+    // first column c >= base at which body a overlaps wall wk AND the back-tracked time of impact
+    // is valid (approaching at column c-1, inside this step); kGrid+1 when there is none.
+    // The velocity of a segment is monotone, so q(c) is convex or concave and the first overlap
+    // column is found by bisection on a monotone predicate; the reference's per-column test
+    // (:374-463) then runs from that column on.
+    RGS_DEV int search_wall(int a, int wk, int base, T &t_out) const {
+        const Axis A = axis_of(a, wk);
+        const T lim = wk >= 2 ? P.lim_x[A.ty] : P.lim_y[A.ty];
+        int c0 = base;
+        const bool bis = A.fl <= base;
+        if (bis) {  // no pending correctOverlap jump inside the range: q is convex / concave
+            T q, v;
+            axis_at(A, base, q, v);
+            if (q < lim) {
+                const bool falling = A.w0 > T(0);  // velocity decreases along the segment (concave q)
+                int lo = base + 1, hi = kGrid + 1;
 #pragma unroll 1
-        for (int c = base; c <= kGrid; ++c) {
-            if (p >= lim && vm > T(0)) {
+                for (int it = 0; it < 6; ++it) {
+                    const int mid = (lo + hi) >> 1;
+                    if (lo < hi) {
+                        axis_at(A, mid, q, v);
+                        if (q >= lim || (falling && v <= T(0))) hi = mid; else lo = mid + 1;
+                    }
+                }
+                c0 = lo;
+                if (c0 > kGrid) return kGrid + 1;
+            }
+        }
+        T px, py, vx, vy;
+        eval(a, c0 - 1, px, py, vx, vy);
+        const T sgn = (wk == WALL_UP || wk == WALL_RIGHT) ? T(1) : T(-1);
+        T pm = sgn * (wk >= 2 ? px : py), vm = sgn * (wk >= 2 ? vx : vy);
+        eval(a, c0, px, py, vx, vy);
+        T p = sgn * (wk >= 2 ? px : py);
+        T w = sgn * (wk >= 2 ? vx : vy) - A.u;
+        const T R = tab->e[A.ty][1].g, k1 = tab->e[A.ty][1].k, uh = A.u * P.d.dt_col;
+        const T doff = A.off_t - A.off_b;
+        bool was_over = false;
+#pragma unroll 1
+        for (int c = c0; c <= kGrid; ++c) {
+            const bool over = p >= lim;
+            if (over && vm > T(0)) {
                 const T tc = P.d.dt_col * T(c - 1) + tmax(T(0), (lim - pm) / vm);
                 if (tc < P.d.dt) { t_out = tc; return c; }
             }
+            // left the wall again on a concave arc with no pending jump: it cannot come back
+            if (was_over && !over && A.fl <= c && w > T(0)) break;
+            if (bis && !over && !was_over && c > c0) break;  // bisection: c0 was the only possible first overlap
+            was_over = was_over || over;
             pm = p;
-            vm = u + w;
+            vm = A.u + w;
             p = fm(w, k1, p + uh);
             w = w * R;
-            if (c + 1 == fl) p += doff;
+            if (c + 1 == A.fl) p += doff;
         }
         return kGrid + 1;
     }
 
-    // same for the pair (a, b); the time is symmetric in (a, b) as in the reference (:482-494)
+    // same for the pair (a, b); the time is symmetric in (a, b) as in the reference (:482-494).
+    // Conservative advancement: while the bodies are apart, the relative speed bound S of the two
+    // segments says how many columns can be skipped before they could touch.
     RGS_DEV int search_pair(int a, int b, int base, T &t_out) const {
         const int tya = (a == PK), tyb = (b == PK);
         const T thr = P.d.ov_le[tya][tyb], sigma = P.d.sig[tya][tyb];
-        T amx, amy, amvx, amvy, bmx, bmy, bmvx, bmvy, ax, ay, avx, avy, bx, by, bvx, bvy;
-        eval(a, base - 1, amx, amy, amvx, amvy);
-        eval(b, base - 1, bmx, bmy, bmvx, bmvy);
-        eval(a, base, ax, ay, avx, avy);
-        eval(b, base, bx, by, bvx, bvy);
-        const T uax = s.F(S::CMD + 2 * a), uay = s.F(S::CMD + 2 * a + 1), ubx = s.F(S::CMD + 2 * b), uby = s.F(S::CMD + 2 * b + 1);
-        T wax = avx - uax, way = avy - uay, wbx = bvx - ubx, wby = bvy - uby;
         const T h = P.d.dt_col;
-        const T Ra = tab->g[tya][1], ka = tab->k[tya][1], Rb = tab->g[tyb][1], kb = tab->k[tyb][1];
-        const T uaxh = uax * h, uayh = uay * h, ubxh = ubx * h, ubyh = uby * h;
-        const int fla = s.I(S::FL + a), flb = s.I(S::FL + b);
-        const T dax = s.F(S::OFF + 4 * a) - s.F(S::OFF + 4 * a + 2), day = s.F(S::OFF + 4 * a + 1) - s.F(S::OFF + 4 * a + 3);
-        const T dbx = s.F(S::OFF + 4 * b) - s.F(S::OFF + 4 * b + 2), dby = s.F(S::OFF + 4 * b + 1) - s.F(S::OFF + 4 * b + 3);
+        T inv_sh;  // 0.98 / (S h); 0 when a correctOverlap jump is pending (no skipping)
+        {
+            T sx, sy;
+            {
+                const T va0 = s.F(S::SP + 4 * a + 2), ua = s.F(S::CMD + 2 * a), vb0 = s.F(S::SP + 4 * b + 2), ub = s.F(S::CMD + 2 * b);
+                const T va1 = fm(va0 - ua, tab->e[tya][kGrid - s.I(S::CS + a)].g, ua), vb1 = fm(vb0 - ub, tab->e[tyb][kGrid - s.I(S::CS + b)].g, ub);
+                const T alo = tmin(va0, va1), ahi = tmax(va0, va1), blo = tmin(vb0, vb1), bhi = tmax(vb0, vb1);
+                sx = tmax(ahi - blo, bhi - alo);
+            }
+            {
+                const T va0 = s.F(S::SP + 4 * a + 3), ua = s.F(S::CMD + 2 * a + 1), vb0 = s.F(S::SP + 4 * b + 3), ub = s.F(S::CMD + 2 * b + 1);
+                const T va1 = fm(va0 - ua, tab->e[tya][kGrid - s.I(S::CS + a)].g, ua), vb1 = fm(vb0 - ub, tab->e[tyb][kGrid - s.I(S::CS + b)].g, ub);
+                const T alo = tmin(va0, va1), ahi = tmax(va0, va1), blo = tmin(vb0, vb1), bhi = tmax(vb0, vb1);
+                sy = tmax(ahi - blo, bhi - alo);
+            }
+            const T S2 = fm(sx, sx, sy * sy);
+            const bool jump = s.I(S::FL + a) > base || s.I(S::FL + b) > base;
+            inv_sh = jump ? T(0) : T(0.98) / (T(sqrt(S2)) * h + T(1.0e-12));
+        }
+        int c = base;
 #pragma unroll 1
-        for (int c = base; c <= kGrid; ++c) {
+        while (c <= kGrid) {
+            T ax, ay, avx, avy, bx, by, bvx, bvy;
+            eval(a, c, ax, ay, avx, avy);
+            eval(b, c, bx, by, bvx, bvy);
             const T ex = ax - bx, ey = ay - by;
-            if (fm(ex, ex, ey * ey) <= thr) {
-                const T dpx = bmx - amx, dpy = bmy - amy, dvx = bmvx - amvx, dvy = bmvy - amvy;
+            const T ssq = fm(ex, ex, ey * ey);
+            if (ssq <= thr) {
+                eval(a, c - 1, ax, ay, avx, avy);
+                eval(b, c - 1, bx, by, bvx, bvy);
+                const T dpx = bx - ax, dpy = by - ay, dvx = bvx - avx, dvy = bvy - avy;
                 const T dpdv = fm(dpx, dvx, dpy * dvy), dvdv = fm(dvx, dvx, dvy * dvy), dpdp = fm(dpx, dpx, dpy * dpy);
                 const T d = dpdv * dpdv - dvdv * (dpdp - sigma * sigma);
                 if (dpdv < T(0) && d >= T(0)) {
                     const T tc = h * T(c - 1) + tmax(T(0), -(dpdv + T(sqrt(d))) / dvdv);
                     if (tc < P.d.dt) { t_out = tc; return c; }
                 }
+                ++c;
+            } else {
+                const T skip = (T(sqrt(ssq)) - sigma) * inv_sh;
+                c += 1 + (int)tmin(skip, T(64));
             }
-            amx = ax; amy = ay; amvx = uax + wax; amvy = uay + way;
-            bmx = bx; bmy = by; bmvx = ubx + wbx; bmvy = uby + wby;
-            ax = fm(wax, ka, ax + uaxh); ay = fm(way, ka, ay + uayh);
-            bx = fm(wbx, kb, bx + ubxh); by = fm(wby, kb, by + ubyh);
-            wax *= Ra; way *= Ra; wbx *= Rb; wby *= Rb;
-            if (c + 1 == fla) { ax += dax; ay += day; }
-            if (c + 1 == flb) { bx += dbx; by += dby; }
         }
         return kGrid + 1;
     }
@@ -361,51 +430,71 @@ struct LaneGame {
         }
     }
 
-    // correctOverlap on the columns after an impact (:285-297): march the pair from its new
-    // segments, record the position offsets
+    // correctOverlap on the columns after an impact (:285-297): visit the columns of the pair's new
+    // segments where it can still overlap (conservative advancement on the relative speed bound,
+    // as in search_pair), record the position offsets
     RGS_DEV void march_pair(int bi, int bj, int base, long long *ev) const {
         const int tyi = (bi == PK), tyj = (bj == PK);
-        T ax = s.F(S::SP + 4 * bi), ay = s.F(S::SP + 4 * bi + 1), bx = s.F(S::SP + 4 * bj), by = s.F(S::SP + 4 * bj + 1);
-        const T uax = s.F(S::CMD + 2 * bi), uay = s.F(S::CMD + 2 * bi + 1), ubx = s.F(S::CMD + 2 * bj), uby = s.F(S::CMD + 2 * bj + 1);
-        T wax = s.F(S::SP + 4 * bi + 2) - uax, way = s.F(S::SP + 4 * bi + 3) - uay;
-        T wbx = s.F(S::SP + 4 * bj + 2) - ubx, wby = s.F(S::SP + 4 * bj + 3) - uby;
-        const T h = P.d.dt_col;
-        const T Ra = tab->g[tyi][1], ka = tab->k[tyi][1], Rb = tab->g[tyj][1], kb = tab->k[tyj][1];
-        const T uaxh = uax * h, uayh = uay * h, ubxh = ubx * h, ubyh = uby * h;
-        const T thr = P.d.ov_lt[tyi][tyj];
+        const T thr = P.d.ov_lt[tyi][tyj], sigma = P.d.sig[tyi][tyj];
+        T inv_sh;
+        {
+            const int rem = kGrid - base;
+            T sx, sy;
+            {
+                const T va0 = s.F(S::SP + 4 * bi + 2), ua = s.F(S::CMD + 2 * bi), vb0 = s.F(S::SP + 4 * bj + 2), ub = s.F(S::CMD + 2 * bj);
+                const T va1 = fm(va0 - ua, tab->e[tyi][rem].g, ua), vb1 = fm(vb0 - ub, tab->e[tyj][rem].g, ub);
+                sx = tmax(tmax(va0, va1) - tmin(vb0, vb1), tmax(vb0, vb1) - tmin(va0, va1));
+            }
+            {
+                const T va0 = s.F(S::SP + 4 * bi + 3), ua = s.F(S::CMD + 2 * bi + 1), vb0 = s.F(S::SP + 4 * bj + 3), ub = s.F(S::CMD + 2 * bj + 1);
+                const T va1 = fm(va0 - ua, tab->e[tyi][rem].g, ua), vb1 = fm(vb0 - ub, tab->e[tyj][rem].g, ub);
+                sy = tmax(tmax(va0, va1) - tmin(vb0, vb1), tmax(vb0, vb1) - tmin(va0, va1));
+            }
+            inv_sh = T(0.98) / (T(sqrt(fm(sx, sx, sy * sy))) * P.d.dt_col + T(1.0e-12));
+        }
+        int c = base + 1;
 #pragma unroll 1
-        for (int c = base + 1; c <= kGrid; ++c) {
-            ax = fm(wax, ka, ax + uaxh); ay = fm(way, ka, ay + uayh);
-            bx = fm(wbx, kb, bx + ubxh); by = fm(wby, kb, by + ubyh);
-            wax *= Ra; way *= Ra; wbx *= Rb; wby *= Rb;
+        while (c <= kGrid) {
+            T ax, ay, avx, avy, bx, by, bvx, bvy;
+            eval(bi, c, ax, ay, avx, avy);
+            eval(bj, c, bx, by, bvx, bvy);
             const T dx = bx - ax, dy = by - ay;
             const T ssq = fm(dx, dx, dy * dy);
             if (ssq <= thr) {
-                const T overlap = P.d.sig[tyi][tyj] - T(sqrt(ssq));
+                const T overlap = sigma - T(sqrt(ssq));
                 const T si = P.d.fix_coef[tyi][tyj] * overlap, sj = P.d.fix_coef[tyj][tyi] * overlap;
                 const T fax = -(si * dx), fay = -(si * dy), fbx = sj * dx, fby = sj * dy;
-                ax += fax; ay += fay; bx += fbx; by += fby;
-                s.F(S::OFF + 4 * bi + 2) = s.F(S::OFF + 4 * bi); s.F(S::OFF + 4 * bi + 3) = s.F(S::OFF + 4 * bi + 1);
+                // the offsets in force before this column stay valid for the columns before it
+                const bool fresh_i = s.I(S::FL + bi) < c, fresh_j = s.I(S::FL + bj) < c;
+                if (fresh_i) { s.F(S::OFF + 4 * bi + 2) = s.F(S::OFF + 4 * bi); s.F(S::OFF + 4 * bi + 3) = s.F(S::OFF + 4 * bi + 1); }
+                if (fresh_j) { s.F(S::OFF + 4 * bj + 2) = s.F(S::OFF + 4 * bj); s.F(S::OFF + 4 * bj + 3) = s.F(S::OFF + 4 * bj + 1); }
                 s.F(S::OFF + 4 * bi) += fax; s.F(S::OFF + 4 * bi + 1) += fay;
-                s.F(S::OFF + 4 * bj + 2) = s.F(S::OFF + 4 * bj); s.F(S::OFF + 4 * bj + 3) = s.F(S::OFF + 4 * bj + 1);
                 s.F(S::OFF + 4 * bj) += fbx; s.F(S::OFF + 4 * bj + 1) += fby;
                 s.I(S::FL + bi) = c;
                 s.I(S::FL + bj) = c;
                 ev[RGS_EV_OVERLAP_FIXES]++;
+                ++c;
+            } else {
+                const T skip = (T(sqrt(ssq)) - sigma) * inv_sh;
+                c += 1 + (int)tmin(skip, T(64));
             }
         }
     }
-    // same for a body and the wall it hit (:329-340)
+    // same for a body and the wall it hit (:329-340).  q(c) is convex or concave on the new
+    // segment and starts inside the limit, so it can only overlap again if its last column does.
     RGS_DEV void march_wall(int bi, int wk, int base, long long *ev) const {
-        const int ty = (bi == PK);
+        const Axis A = axis_of(bi, wk);
         const int ax = wk >= 2 ? 0 : 1;
         const T sgn = (wk == WALL_UP || wk == WALL_RIGHT) ? T(1) : T(-1);
-        const T lim = ax == 0 ? P.lim_x[ty] : P.lim_y[ty];
-        const T lim_in = ax == 0 ? P.lim_x_in[ty] : P.lim_y_in[ty];
-        const T u = sgn * s.F(S::CMD + 2 * bi + ax);
-        T p = sgn * s.F(S::SP + 4 * bi + ax);
-        T w = sgn * s.F(S::SP + 4 * bi + 2 + ax) - u;
-        const T R = tab->g[ty][1], k1 = tab->k[ty][1], uh = u * P.d.dt_col;
+        const T lim = ax == 0 ? P.lim_x[A.ty] : P.lim_y[A.ty];
+        const T lim_in = ax == 0 ? P.lim_x_in[A.ty] : P.lim_y_in[A.ty];
+        {
+            T qe, ve;
+            axis_at(A, kGrid, qe, ve);
+            if (qe < lim) return;
+        }
+        T p = A.sp, w = A.w0;
+        const T R = tab->e[A.ty][1].g, k1 = tab->e[A.ty][1].k, uh = A.u * P.d.dt_col;
 #pragma unroll 1
         for (int c = base + 1; c <= kGrid; ++c) {
             p = fm(w, k1, p + uh);

