@@ -5,7 +5,7 @@
  * include/SimState.h:7-59), generalised from 2v2 to n-v-n and instrumented with event counters.
  * It is pinned bit-for-bit (all 22 state doubles, clock and damage, every step) against the
  * unmodified reference compiled in place (oracle/_ref, see oracle/Makefile) by
- * tests/test_oracle_vs_reference.py and by the committed fixtures in tests/golden/.
+ * tests/test_oracle.py and by the committed fixtures in tests/golden/.
  *
  * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
  * load this library.  The product path (robo_game_sim_b200/) never does.
