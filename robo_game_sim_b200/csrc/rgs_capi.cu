@@ -70,6 +70,7 @@ struct rgs_batch {
     rgs_params p{};
     int n_team = 2, E = 5, srec = 22, dmg_rec = 16;
     bool warp_k2 = false;  // RGS_K2_WARP=1: the superseded warp-per-game throughput kernel (A/B measurements only)
+    bool lane_k2 = false;  // RGS_K2_LANE=1: the one-lane-per-game kernel without block compaction (A/B; teams > 3 always)
     double *state = nullptr, *clock = nullptr, *damage = nullptr;
     long long *events = nullptr, *stats = nullptr;
     // staging for rgs_batch_run_host
@@ -124,11 +125,13 @@ int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64
         break;
     case RGS_MODE_FAST_F32:
         e = b->warp_k2 ? rgs::launch_rollout_fast_f32(b->n_team, b->p, A, stream, b->sm_count)
-                       : rgs::launch_rollout_lane_f32(b->n_team, b->p, A, stream, b->sm_count);
+            : (b->lane_k2 || b->n_team > 3) ? rgs::launch_rollout_lane_f32(b->n_team, b->p, A, stream, b->sm_count)
+                                            : rgs::launch_rollout_phase_f32(b->n_team, b->p, A, stream, b->sm_count);
         break;
     default:
         e = b->warp_k2 ? rgs::launch_rollout_fast_f64(b->n_team, b->p, A, stream, b->sm_count)
-                       : rgs::launch_rollout_lane_f64(b->n_team, b->p, A, stream, b->sm_count);
+            : (b->lane_k2 || b->n_team > 3) ? rgs::launch_rollout_lane_f64(b->n_team, b->p, A, stream, b->sm_count)
+                                            : rgs::launch_rollout_phase_f64(b->n_team, b->p, A, stream, b->sm_count);
         break;
     }
     if (e != cudaSuccess) return cuda_fail(e, "rollout kernel launch");
@@ -210,6 +213,8 @@ int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_par
     {
         const char *w = std::getenv("RGS_K2_WARP");
         b->warp_k2 = w && w[0] == '1';
+        const char *l = std::getenv("RGS_K2_LANE");
+        b->lane_k2 = l && l[0] == '1';
     }
     cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
     const size_t n = (size_t)(n_games > 0 ? n_games : 1);

@@ -16,9 +16,14 @@ cudaError_t launch_rollout_exact(int n_team, const DevParams<double> &P, const R
 cudaError_t launch_rollout_fast_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 cudaError_t launch_rollout_fast_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 
-// K2, one lane per game (rgs_lane_kernel.cu): the throughput kernel the FAST modes run
+// K2, one lane per game (rgs_lane_kernel.cu): teams of more than 3, and RGS_K2_LANE=1 (A/B)
 cudaError_t launch_rollout_lane_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 cudaError_t launch_rollout_lane_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
+
+// K2, phased block kernel (rgs_phase_kernel.cu): same arithmetic as the lane kernel, narrow-phase items and
+// popped events compacted across the CTA; the kernel the FAST modes run for teams of up to 3
+cudaError_t launch_rollout_phase_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
+cudaError_t launch_rollout_phase_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 
 // K4: per-batch statistics vector int64[RGS_N_STATS] (rgs_aux_kernels.cu)
 cudaError_t launch_stats(int n_team, int64_t n_games, const double *state, const long long *events, int winning_score,

@@ -512,6 +512,116 @@ struct LaneGame {
         }
     }
 
+    // ---- execute one popped event (carryOutFirstCollision :237-345): advance the bodies to the time of
+    // impact, resolve, start their new segments at column `base`, correctOverlap on the later columns.
+    // Returns the second body to re-scan (-1 for a wall event); goal = 1 (team A) / 2 (team B) / 0.
+    RGS_DEV int resolve(int ei, int ej, int ekind, T et, int &base, int &goal, long long *ev, double *dmg, long long live) const {
+        int rj = -1;
+        goal = 0;
+        {
+            int nb = (int)floor(et / P.d.dt_col) + 1;  // :237
+            if (nb > kGrid) { nb = kGrid; ev[RGS_EV_BASE_CLAMP]++; }
+            if (nb > base) base = nb;  // event times never run backwards by more than a rounding
+        }
+        const T dt_t = et - P.d.dt_col * T(base - 1);  // :254 / :308
+        const T h_rest = P.d.dt_col - dt_t;
+        const int tyi = (ei == PK);
+        T qix, qiy, qvix, qviy;
+        eval(ei, base - 1, qix, qiy, qvix, qviy);
+        T pix = qix, piy = qiy, vix = qvix, viy = qviy;
+        const T uix = s.F(S::CMD + 2 * ei), uiy = s.F(S::CMD + 2 * ei + 1);
+        advance_axis(pix, vix, uix, dt_t, P.neg_inv_tau[tyi]);
+        advance_axis(piy, viy, uiy, dt_t, P.neg_inv_tau[tyi]);
+        if (ekind == PAIR) {  // :242-299
+            const int tyj = (ej == PK);
+            T qjx, qjy, qvjx, qvjy;
+            eval(ej, base - 1, qjx, qjy, qvjx, qvjy);
+            T pjx = qjx, pjy = qjy, vjx = qvjx, vjy = qvjy;
+            const T ujx = s.F(S::CMD + 2 * ej), ujy = s.F(S::CMD + 2 * ej + 1);
+            advance_axis(pjx, vjx, ujx, dt_t, P.neg_inv_tau[tyj]);
+            advance_axis(pjy, vjy, ujy, dt_t, P.neg_inv_tau[tyj]);
+            {  // residual overlap of the constant-velocity impact-time estimate :259-265
+                const T dx = pjx - pix, dy = pjy - piy;
+                const T ssq = dx * dx + dy * dy;
+                if (ssq <= P.d.ov_lt[tyi][tyj]) {
+                    const T overlap = P.d.sig[tyi][tyj] - T(sqrt(ssq));
+                    const T si = P.d.hit_coef[tyi][tyj] * overlap, sj = P.d.hit_coef[tyj][tyi] * overlap;
+                    pix -= si * dx; piy -= si * dy;
+                    pjx += sj * dx; pjy += sj * dy;
+                }
+            }
+            {  // elastic impulse :268-274
+                const T dvx = vix - vjx, dvy = viy - vjy, dpx = pix - pjx, dpy = piy - pjy;
+                const T dot = fm(dvx, dpx, dvy * dpy), nn = fm(dpx, dpx, dpy * dpy);
+                const T fi = P.d.imp_coef[tyi][tyj] * dot / nn, fj = P.d.imp_coef[tyj][tyi] * dot / nn;
+                if (ei != PK && ej != PK) {  // damage :277-282
+                    const double dv_sq = 0.01 * ((double)dvx * (double)dvx + (double)dvy * (double)dvy);
+                    dmg[ei * NP + ej] += (double)P.d.mass[tyi] * dv_sq;
+                    dmg[ej * NP + ei] += (double)P.d.mass[tyj] * dv_sq;
+                    ev[RGS_EV_PLAYER_PLAYER]++;
+                } else {
+                    ev[RGS_EV_PLAYER_PUCK]++;
+                }
+                vix -= fi * dpx; viy -= fi * dpy;
+                vjx += fj * dpx; vjy += fj * dpy;
+            }
+            advance_axis(pix, vix, uix, h_rest, P.neg_inv_tau[tyi]);
+            advance_axis(piy, viy, uiy, h_rest, P.neg_inv_tau[tyi]);
+            advance_axis(pjx, vjx, ujx, h_rest, P.neg_inv_tau[tyj]);
+            advance_axis(pjy, vjy, ujy, h_rest, P.neg_inv_tau[tyj]);
+            {  // correctOverlap at column base :287
+                const T dx = pjx - pix, dy = pjy - piy;
+                const T ssq = dx * dx + dy * dy;
+                if (ssq <= P.d.ov_lt[tyi][tyj]) {
+                    const T overlap = P.d.sig[tyi][tyj] - T(sqrt(ssq));
+                    const T si = P.d.fix_coef[tyi][tyj] * overlap, sj = P.d.fix_coef[tyj][tyi] * overlap;
+                    pix -= si * dx; piy -= si * dy;
+                    pjx += sj * dx; pjy += sj * dy;
+                    ev[RGS_EV_OVERLAP_FIXES]++;
+                }
+            }
+            start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
+            start_segment(ej, base, pjx, pjy, vjx, vjy, qjx, qjy, qvjx, qvjy);
+            march_pair(ei, ej, base, ev);
+            update_bbox(ej);
+            rj = ej;
+        } else {  // wall :300-343
+            switch (ekind) {  // flip only while still moving into the wall :312-318
+            case WALL_UP: if (viy > T(0)) viy = -viy; break;
+            case WALL_DOWN: if (viy < T(0)) viy = -viy; break;
+            case WALL_RIGHT: if (vix > T(0)) vix = -vix; break;
+            default: if (vix < T(0)) vix = -vix; break;
+            }
+            const bool is_goal = (ei == PK) && (ekind == WALL_LEFT || ekind == WALL_RIGHT) && piy < P.d.half_goal &&
+                                 piy > -P.d.half_goal;  // :321-322
+            if (is_goal) {
+                goal = ekind == WALL_RIGHT ? 1 : 2;
+                ev[goal == 1 ? RGS_EV_GOALS_A : RGS_EV_GOALS_B]++;
+                pix = piy = vix = viy = T(0);  // puck reset :325
+            } else {
+                advance_axis(pix, vix, uix, h_rest, P.neg_inv_tau[tyi]);
+                advance_axis(piy, viy, uiy, h_rest, P.neg_inv_tau[tyi]);
+                {  // correctOverlap(wall) at column base :334 (folded limit, kept strictly inside)
+                    const bool xa = ekind >= WALL_RIGHT;
+                    const T sgn = (ekind == WALL_UP || ekind == WALL_RIGHT) ? T(1) : T(-1);
+                    const T lim = xa ? P.lim_x[tyi] : P.lim_y[tyi], lim_in = xa ? P.lim_x_in[tyi] : P.lim_y_in[tyi];
+                    const T q = sgn * (xa ? pix : piy);
+                    if (q >= lim) {
+                        const T qc = sgn * tmin(q - P.d.wall_fix * (q - lim), lim_in);
+                        if (xa) pix = qc; else piy = qc;
+                        ev[RGS_EV_OVERLAP_FIXES]++;
+                    }
+                }
+            }
+            ev[RGS_EV_WALL_UP + ekind]++;
+            start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
+            if (!is_goal) march_wall(ei, ekind, base, ev);
+        }
+        update_bbox(ei);
+        hash_event(ev, live, ekind, ei, ej, goal);
+        return rj;
+    }
+
     // ---- one game-step (GameSim::updateSim :126-171); SP/CMD hold the state and the commands ----
     // returns the event-loop counter of the step (1 when nothing happened)
     RGS_DEV int step(double &sa, double &sb, long long *ev, double *dmg, long long live) const {
@@ -560,109 +670,12 @@ struct LaneGame {
                     ++counter;
                     continue;
                 }
-                {
-                    int nb = (int)floor(et / P.d.dt_col) + 1;  // :237
-                    if (nb > kGrid) { nb = kGrid; ev[RGS_EV_BASE_CLAMP]++; }
-                    if (nb > base) base = nb;  // event times never run backwards by more than a rounding
-                }
-                const T dt_t = et - P.d.dt_col * T(base - 1);  // :254 / :308
-                const T h_rest = P.d.dt_col - dt_t;
                 int goal = 0;
-                const int tyi = (ei == PK);
-                T qix, qiy, qvix, qviy;
-                eval(ei, base - 1, qix, qiy, qvix, qviy);
-                T pix = qix, piy = qiy, vix = qvix, viy = qviy;
-                const T uix = s.F(S::CMD + 2 * ei), uiy = s.F(S::CMD + 2 * ei + 1);
-                advance_axis(pix, vix, uix, dt_t, P.neg_inv_tau[tyi]);
-                advance_axis(piy, viy, uiy, dt_t, P.neg_inv_tau[tyi]);
-                if (ekind == PAIR) {  // :242-299
-                    const int tyj = (ej == PK);
-                    T qjx, qjy, qvjx, qvjy;
-                    eval(ej, base - 1, qjx, qjy, qvjx, qvjy);
-                    T pjx = qjx, pjy = qjy, vjx = qvjx, vjy = qvjy;
-                    const T ujx = s.F(S::CMD + 2 * ej), ujy = s.F(S::CMD + 2 * ej + 1);
-                    advance_axis(pjx, vjx, ujx, dt_t, P.neg_inv_tau[tyj]);
-                    advance_axis(pjy, vjy, ujy, dt_t, P.neg_inv_tau[tyj]);
-                    {  // residual overlap of the constant-velocity impact-time estimate :259-265
-                        const T dx = pjx - pix, dy = pjy - piy;
-                        const T ssq = dx * dx + dy * dy;
-                        if (ssq <= P.d.ov_lt[tyi][tyj]) {
-                            const T overlap = P.d.sig[tyi][tyj] - T(sqrt(ssq));
-                            const T si = P.d.hit_coef[tyi][tyj] * overlap, sj = P.d.hit_coef[tyj][tyi] * overlap;
-                            pix -= si * dx; piy -= si * dy;
-                            pjx += sj * dx; pjy += sj * dy;
-                        }
-                    }
-                    {  // elastic impulse :268-274
-                        const T dvx = vix - vjx, dvy = viy - vjy, dpx = pix - pjx, dpy = piy - pjy;
-                        const T dot = fm(dvx, dpx, dvy * dpy), nn = fm(dpx, dpx, dpy * dpy);
-                        const T fi = P.d.imp_coef[tyi][tyj] * dot / nn, fj = P.d.imp_coef[tyj][tyi] * dot / nn;
-                        if (ei != PK && ej != PK) {  // damage :277-282
-                            const double dv_sq = 0.01 * ((double)dvx * (double)dvx + (double)dvy * (double)dvy);
-                            dmg[ei * NP + ej] += (double)P.d.mass[tyi] * dv_sq;
-                            dmg[ej * NP + ei] += (double)P.d.mass[tyj] * dv_sq;
-                            ev[RGS_EV_PLAYER_PLAYER]++;
-                        } else {
-                            ev[RGS_EV_PLAYER_PUCK]++;
-                        }
-                        vix -= fi * dpx; viy -= fi * dpy;
-                        vjx += fj * dpx; vjy += fj * dpy;
-                    }
-                    advance_axis(pix, vix, uix, h_rest, P.neg_inv_tau[tyi]);
-                    advance_axis(piy, viy, uiy, h_rest, P.neg_inv_tau[tyi]);
-                    advance_axis(pjx, vjx, ujx, h_rest, P.neg_inv_tau[tyj]);
-                    advance_axis(pjy, vjy, ujy, h_rest, P.neg_inv_tau[tyj]);
-                    {  // correctOverlap at column base :287
-                        const T dx = pjx - pix, dy = pjy - piy;
-                        const T ssq = dx * dx + dy * dy;
-                        if (ssq <= P.d.ov_lt[tyi][tyj]) {
-                            const T overlap = P.d.sig[tyi][tyj] - T(sqrt(ssq));
-                            const T si = P.d.fix_coef[tyi][tyj] * overlap, sj = P.d.fix_coef[tyj][tyi] * overlap;
-                            pix -= si * dx; piy -= si * dy;
-                            pjx += sj * dx; pjy += sj * dy;
-                            ev[RGS_EV_OVERLAP_FIXES]++;
-                        }
-                    }
-                    start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
-                    start_segment(ej, base, pjx, pjy, vjx, vjy, qjx, qjy, qvjx, qvjy);
-                    march_pair(ei, ej, base, ev);
-                    update_bbox(ej);
-                    rj = ej;
-                } else {  // wall :300-343
-                    switch (ekind) {  // flip only while still moving into the wall :312-318
-                    case WALL_UP: if (viy > T(0)) viy = -viy; break;
-                    case WALL_DOWN: if (viy < T(0)) viy = -viy; break;
-                    case WALL_RIGHT: if (vix > T(0)) vix = -vix; break;
-                    default: if (vix < T(0)) vix = -vix; break;
-                    }
-                    const bool is_goal = (ei == PK) && (ekind == WALL_LEFT || ekind == WALL_RIGHT) && piy < P.d.half_goal &&
-                                         piy > -P.d.half_goal;  // :321-322
-                    if (is_goal) {
-                        if (ekind == WALL_RIGHT) { sa += 1.0; goal = 1; } else { sb += 1.0; goal = 2; }
-                        ev[goal == 1 ? RGS_EV_GOALS_A : RGS_EV_GOALS_B]++;
-                        scored = true;
-                        pix = piy = vix = viy = T(0);  // puck reset :325
-                    } else {
-                        advance_axis(pix, vix, uix, h_rest, P.neg_inv_tau[tyi]);
-                        advance_axis(piy, viy, uiy, h_rest, P.neg_inv_tau[tyi]);
-                        {  // correctOverlap(wall) at column base :334 (folded limit, kept strictly inside)
-                            const bool xa = ekind >= WALL_RIGHT;
-                            const T sgn = (ekind == WALL_UP || ekind == WALL_RIGHT) ? T(1) : T(-1);
-                            const T lim = xa ? P.lim_x[tyi] : P.lim_y[tyi], lim_in = xa ? P.lim_x_in[tyi] : P.lim_y_in[tyi];
-                            const T q = sgn * (xa ? pix : piy);
-                            if (q >= lim) {
-                                const T qc = sgn * tmin(q - P.d.wall_fix * (q - lim), lim_in);
-                                if (xa) pix = qc; else piy = qc;
-                                ev[RGS_EV_OVERLAP_FIXES]++;
-                            }
-                        }
-                    }
-                    ev[RGS_EV_WALL_UP + ekind]++;
-                    start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
-                    if (!is_goal) march_wall(ei, ekind, base, ev);
+                rj = resolve(ei, ej, ekind, et, base, goal, ev, dmg, live);
+                if (goal) {
+                    if (goal == 1) sa += 1.0; else sb += 1.0;
+                    scored = true;
                 }
-                update_bbox(ei);
-                hash_event(ev, live, ekind, ei, ej, goal);
                 prune(qmask, ei, ej);  // :347-352
                 // re-scan the bodies involved (:355-357, :147): broad phase on their new segments
                 owners = 1u << ei;

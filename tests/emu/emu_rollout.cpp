@@ -9,9 +9,11 @@
 #include "../../robo_game_sim_b200/csrc/rgs_exact.cuh"
 #include "../../robo_game_sim_b200/csrc/rgs_fast.cuh"
 #include "../../robo_game_sim_b200/csrc/rgs_lane.cuh"
+#include "../../robo_game_sim_b200/csrc/rgs_phase.cuh"
 #include "../../robo_game_sim_b200/csrc/rgs_host_params.h"
 
 #include <memory>
+#include <vector>
 
 namespace {
 
@@ -45,6 +47,51 @@ void run_lane(const rgs_params &p, const rgs::RunArgs &A) {
     for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT>(P, A, tab.get(), s, g);
 }
 
+// The phased block kernel (rgs_phase.cuh), one block of `n_threads` slots; the threads of a phase are
+// stepped one after the other, the barriers of rollout_phase_kernel are the ends of the loops.
+// RGS_EMU_PHASE="threads,records,item_capacity" overrides the geometry (pool-exhaustion and
+// list-overflow paths).
+template <typename T, int NT>
+void run_phase(const rgs_params &p, const rgs::RunArgs &A) {
+    using Sh = rgs::PhaseShared<T, NT>;
+    int n_threads = 64, n_rec = 32, cap = 128;
+    if (const char *g = std::getenv("RGS_EMU_PHASE")) std::sscanf(g, "%d,%d,%d", &n_threads, &n_rec, &cap);
+    const rgs::FastParams<T> P = rgs::make_fast_params<T>(p);
+    std::vector<unsigned char> raw(Sh::bytes(n_rec, cap) + 16);
+    unsigned char *base = raw.data() + ((16 - (reinterpret_cast<uintptr_t>(raw.data()) & 15)) & 15);
+    Sh sh;
+    sh.carve(base, n_rec, cap);
+    auto *tab = reinterpret_cast<rgs::LaneTab<T> *>(base);
+    for (int ty = 0; ty < 2; ++ty)
+        for (int i = 0; i < rgs::kCols; ++i) { tab->e[ty][i].g = P.tab_g[ty][i]; tab->e[ty][i].k = P.tab_k[ty][i]; }
+    for (int i = 0; i < n_rec; ++i) sh.free_stack[i] = i;
+    for (int i = 0; i < 8; ++i) sh.ctr[i] = i == Sh::FREE_TOP ? n_rec : 0;
+    const rgs::PhaseKernel<T, NT> K(P, A, sh);
+    std::vector<rgs::PhaseSlot<T, NT>> ts(n_threads);
+    for (int t = 0; t < n_threads; ++t) K.init_slot(ts[t], t);
+    auto any_rec = [&] { for (auto &s : ts) if (s.rec >= 0) return true; return false; };
+    auto all_done = [&] { for (auto &s : ts) if (!K.slot_done(s)) return false; return true; };
+    for (;;) {
+        for (int t = 0; t < n_threads; ++t) K.head(ts[t], n_threads);
+        bool more = any_rec();
+        for (int t = 0; t < n_threads; ++t) K.release_held(ts[t]);
+        if (!more) {
+            if (all_done()) break;
+            continue;
+        }
+        for (int r = 0; r < rgs::kPhaseRounds && more; ++r) {
+            for (int t = 0; t < n_threads; ++t) K.search(t, n_threads);
+            sh.ctr[Sh::N_WALL] = 0;
+            sh.ctr[Sh::N_PAIR] = 0;
+            for (int t = 0; t < n_threads; ++t) K.pop_phase(ts[t]);
+            for (int t = 0; t < n_threads; ++t) K.resolve_phase(t, n_threads);
+            more = any_rec();
+            sh.ctr[Sh::N_WALL_EV] = 0;
+            sh.ctr[Sh::N_PAIR_EV] = 0;
+        }
+    }
+}
+
 template <int NT>
 void dispatch(const rgs_params &p, const rgs::RunArgs &A) {
     // the FAST modes run the lane body, as librgs_b200.so does; RGS_K2_WARP=1 selects the superseded
@@ -54,6 +101,8 @@ void dispatch(const rgs_params &p, const rgs::RunArgs &A) {
     if (p.mode == RGS_MODE_EXACT_F64) run_exact<NT>(p, A);
     else if (p.mode == RGS_MODE_FAST_F32 && warp_k2) run_fast<float, NT>(p, A);
     else if (p.mode == RGS_MODE_FAST_F64 && warp_k2) run_fast<double, NT>(p, A);
+    else if (p.mode == 34) { if constexpr (NT <= 3) run_phase<float, NT>(p, A); }
+    else if (p.mode == 67) { if constexpr (NT <= 3) run_phase<double, NT>(p, A); }
     else if (p.mode == RGS_MODE_FAST_F32 || p.mode == 33) run_lane<float, NT>(p, A);
     else run_lane<double, NT>(p, A);
 }

@@ -101,3 +101,39 @@ def test_fast_kernel_goal_and_freeze(golden):
         assert tr[3, 1] == 0 and tr[4, 1] == 1.0 and np.all(tr[4, 3:7] == 0.0)
         assert e["events"][0, tl.EV["DECIDED_STEP"]] == 5 and e["events"][0, tl.EV["LIVE_STEPS"]] == 5
         assert e["t"][0] == pytest.approx(0.25)
+
+
+# ---- K2 phased block kernel (rgs_phase.cuh): same bits as the one-lane-per-game body ----
+MODE_PHASE_F32, MODE_PHASE_F64 = 34, 67   # emulator-only selectors (librgs_b200.so picks the kernel itself)
+
+
+@pytest.mark.parametrize("geometry", [None, "64,4,8", "32,1,1", "7,3,2", "256,128,512"])
+@pytest.mark.parametrize("n_team", [1, 2, 3])
+def test_phase_kernel_equals_lane_kernel(monkeypatch, geometry, n_team):
+    """Block-compacted schedule vs one lane per game: every state double, clock, damage, event record
+    (incl. the order-sensitive event hash) and trajectory record identical, fp32 and fp64, also
+    when the record pool runs dry (slots retry the step) and the item lists overflow (items searched
+    on the spot), for any block size."""
+    if geometry:
+        monkeypatch.setenv("RGS_EMU_PHASE", geometry)
+    n, steps, hold = (600 if n_team == 2 else 150), 120, 10
+    x0, acts = tl.synth_inputs(5, 0, n, n_team, steps // hold)
+    s0 = tl.oracle_reset(tl.default_params(n_team=n_team), x0)
+    for lane_mode, phase_mode in ((tl.MODE_FAST_F32, MODE_PHASE_F32), (tl.MODE_FAST_F64, MODE_PHASE_F64)):
+        a = tl.emu_rollout(tl.default_params(n_team=n_team, mode=lane_mode, winning_score=1), s0, acts, steps, hold, log_stride=30)
+        b = tl.emu_rollout(tl.default_params(n_team=n_team, mode=phase_mode, winning_score=1), s0, acts, steps, hold, log_stride=30)
+        _assert_same(a, b)
+        assert np.array_equal(a["traj"], b["traj"])
+        assert a["events"][:, 2:8].sum() > 500 and a["events"][:, tl.EV["DECIDED_STEP"]].any()
+
+
+def test_phase_kernel_synth_and_resume():
+    pd = tl.default_params(mode=MODE_PHASE_F32)
+    x0, acts = tl.synth_inputs(77, 123, 40, 2, 6)
+    s0 = tl.oracle_reset(tl.default_params(), x0)
+    a = tl.emu_rollout(pd, s0, acts, 60, 10)
+    b = tl.emu_rollout(pd, s0, None, 60, 10, synth=(77, 123, 0, 10.0))
+    _assert_same(a, b)
+    h = tl.emu_rollout(pd, s0, acts[:, :3], 30, 10)
+    c = tl.emu_rollout(pd, h["state"], acts[:, 3:], 30, 10, t=h["t"], damage=h["damage"], events=h["events"])
+    _assert_same(a, c)
