@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librgs_b200.so")
+# RGS_B200_LIB: another build of the same library (kernel A/B measurements); never a different implementation
+LIB_PATH = os.environ.get("RGS_B200_LIB") or os.path.join(_HERE, "librgs_b200.so")
 
 RGS_OK, RGS_EINVAL, RGS_ECUDA, RGS_ENOMEM, RGS_EUNSUPPORTED = 0, -1, -2, -3, -4
 MODE_EXACT_F64, MODE_FAST_F32, MODE_FAST_F64 = 64, 32, 65

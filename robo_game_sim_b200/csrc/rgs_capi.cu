@@ -70,7 +70,7 @@ struct rgs_batch {
     rgs_params p{};
     int n_team = 2, E = 5, srec = 22, dmg_rec = 16;
     bool warp_k2 = false;  // RGS_K2_WARP=1: the superseded warp-per-game throughput kernel (A/B measurements only)
-    bool lane_k2 = false;  // RGS_K2_LANE=1: the one-lane-per-game kernel without block compaction (A/B; teams > 3 always)
+    bool lane_k2 = true;   // RGS_K2_LANE=0: the phased block kernel (rgs_phase.cuh) instead of one lane per game (A/B; teams <= 3)
     double *state = nullptr, *clock = nullptr, *damage = nullptr;
     long long *events = nullptr, *stats = nullptr;
     // staging for rgs_batch_run_host
@@ -214,7 +214,7 @@ int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_par
         const char *w = std::getenv("RGS_K2_WARP");
         b->warp_k2 = w && w[0] == '1';
         const char *l = std::getenv("RGS_K2_LANE");
-        b->lane_k2 = l && l[0] == '1';
+        b->lane_k2 = !(l && l[0] == '0');
     }
     cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
     const size_t n = (size_t)(n_games > 0 ? n_games : 1);

@@ -16,12 +16,13 @@ cudaError_t launch_rollout_exact(int n_team, const DevParams<double> &P, const R
 cudaError_t launch_rollout_fast_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 cudaError_t launch_rollout_fast_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 
-// K2, one lane per game (rgs_lane_kernel.cu): teams of more than 3, and RGS_K2_LANE=1 (A/B)
+// K2, one lane per game (rgs_lane_kernel.cu): the throughput kernel the FAST modes run
 cudaError_t launch_rollout_lane_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 cudaError_t launch_rollout_lane_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 
-// K2, phased block kernel (rgs_phase_kernel.cu): same arithmetic as the lane kernel, narrow-phase items and
-// popped events compacted across the CTA; the kernel the FAST modes run for teams of up to 3
+// K2, phased block kernel (rgs_phase_kernel.cu): same arithmetic and bit-identical results, narrow-phase items and
+// popped events compacted across the CTA; 37 % fewer instructions but barrier-latency-bound (1.50e9 vs 2.16e9
+// game-steps/s on B200), selected with RGS_K2_LANE=0 for teams of up to 3
 cudaError_t launch_rollout_phase_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 cudaError_t launch_rollout_phase_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 

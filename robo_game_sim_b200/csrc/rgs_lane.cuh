@@ -39,6 +39,14 @@
 #pragma once
 #include "rgs_fast.cuh"
 
+// The rollout kernels are instruction-cache-bound before they are issue-bound (profiles/): the large,
+// rarely-converged narrow-phase and resolution functions are compiled once per kernel and CALLED.
+#if defined(RGS_NOINLINE_BIG) && !defined(RGS_HOST_EMU)
+#define RGS_DEV_BIG __device__ __noinline__
+#else
+#define RGS_DEV_BIG RGS_DEV
+#endif
+
 namespace rgs {
 
 // per-game scratch record: word w of game slot s lives at base[w * stride + s] (bank = lane)
@@ -243,7 +251,7 @@ struct LaneGame {
     // The velocity of a segment is monotone, so q(c) is convex or concave and the first overlap
     // column is found by bisection on a monotone predicate; the reference's per-column test
     // (:374-463) then runs from that column on.
-    RGS_DEV int search_wall(int a, int wk, int base, T &t_out) const {
+    RGS_DEV_BIG int search_wall(int a, int wk, int base, T &t_out) const {
         const Axis A = axis_of(a, wk);
         const T lim = wk >= 2 ? P.lim_x[A.ty] : P.lim_y[A.ty];
         int c0 = base;
@@ -296,10 +304,43 @@ struct LaneGame {
         return kGrid + 1;
     }
 
+    // register copy of what the position of a body at a column depends on (the column loops of
+    // search_pair / march_pair evaluate positions only; same arithmetic as eval())
+    struct PosSeg {
+        T spx, spy, wx, wy, ux, uy, otx, oty, obx, oby;
+        int cs, fl, ty, e;
+    };
+    RGS_DEV PosSeg pos_seg(int e) const {
+        PosSeg g;
+        g.e = e;
+        g.ty = (e == PK);
+        g.cs = s.I(S::CS + e);
+        g.fl = s.I(S::FL + e);
+        g.spx = s.F(S::SP + 4 * e); g.spy = s.F(S::SP + 4 * e + 1);
+        g.ux = s.F(S::CMD + 2 * e); g.uy = s.F(S::CMD + 2 * e + 1);
+        g.wx = s.F(S::SP + 4 * e + 2) - g.ux; g.wy = s.F(S::SP + 4 * e + 3) - g.uy;
+        g.otx = s.F(S::OFF + 4 * e); g.oty = s.F(S::OFF + 4 * e + 1);
+        g.obx = s.F(S::OFF + 4 * e + 2); g.oby = s.F(S::OFF + 4 * e + 3);
+        return g;
+    }
+    RGS_DEV void pos_at(const PosSeg &g, int c, T &px, T &py) const {
+        const int j = c - g.cs;
+        if (j <= 0) {
+            const int w = j < 0 ? S::PRV : S::SP;
+            px = s.F(w + 4 * g.e); py = s.F(w + 4 * g.e + 1);
+            return;
+        }
+        const LaneGK<T> gk = tab->e[g.ty][j];
+        const T tj = P.d.dt_col * T(j);
+        const bool late = c >= g.fl;
+        px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + (late ? g.otx : g.obx);
+        py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + (late ? g.oty : g.oby);
+    }
+
     // same for the pair (a, b); the time is symmetric in (a, b) as in the reference (:482-494).
     // Conservative advancement: while the bodies are apart, the relative speed bound S of the two
     // segments says how many columns can be skipped before they could touch.
-    RGS_DEV int search_pair(int a, int b, int base, T &t_out) const {
+    RGS_DEV_BIG int search_pair(int a, int b, int base, T &t_out) const {
         const int tya = (a == PK), tyb = (b == PK);
         const T thr = P.d.ov_le[tya][tyb], sigma = P.d.sig[tya][tyb];
         const T h = P.d.dt_col;
@@ -323,11 +364,12 @@ struct LaneGame {
             inv_sh = jump ? T(0) : T(0.98) / (T(sqrt(S2)) * h + T(1.0e-12));
         }
         int c = base;
+        const PosSeg ga = pos_seg(a), gb = pos_seg(b);
 #pragma unroll 1
         while (c <= kGrid) {
             T ax, ay, avx, avy, bx, by, bvx, bvy;
-            eval(a, c, ax, ay, avx, avy);
-            eval(b, c, bx, by, bvx, bvy);
+            pos_at(ga, c, ax, ay);
+            pos_at(gb, c, bx, by);
             const T ex = ax - bx, ey = ay - by;
             const T ssq = fm(ex, ex, ey * ey);
             if (ssq <= thr) {
@@ -453,11 +495,12 @@ struct LaneGame {
             inv_sh = T(0.98) / (T(sqrt(fm(sx, sx, sy * sy))) * P.d.dt_col + T(1.0e-12));
         }
         int c = base + 1;
+        PosSeg gi = pos_seg(bi), gj = pos_seg(bj);
 #pragma unroll 1
         while (c <= kGrid) {
-            T ax, ay, avx, avy, bx, by, bvx, bvy;
-            eval(bi, c, ax, ay, avx, avy);
-            eval(bj, c, bx, by, bvx, bvy);
+            T ax, ay, bx, by;
+            pos_at(gi, c, ax, ay);
+            pos_at(gj, c, bx, by);
             const T dx = bx - ax, dy = by - ay;
             const T ssq = fm(dx, dx, dy * dy);
             if (ssq <= thr) {
@@ -472,6 +515,8 @@ struct LaneGame {
                 s.F(S::OFF + 4 * bj) += fbx; s.F(S::OFF + 4 * bj + 1) += fby;
                 s.I(S::FL + bi) = c;
                 s.I(S::FL + bj) = c;
+                gi = pos_seg(bi);
+                gj = pos_seg(bj);
                 ev[RGS_EV_OVERLAP_FIXES]++;
                 ++c;
             } else {
@@ -515,7 +560,7 @@ struct LaneGame {
     // ---- execute one popped event (carryOutFirstCollision :237-345): advance the bodies to the time of
     // impact, resolve, start their new segments at column `base`, correctOverlap on the later columns.
     // Returns the second body to re-scan (-1 for a wall event); goal = 1 (team A) / 2 (team B) / 0.
-    RGS_DEV int resolve(int ei, int ej, int ekind, T et, int &base, int &goal, long long *ev, double *dmg, long long live) const {
+    RGS_DEV_BIG int resolve(int ei, int ej, int ekind, T et, int &base, int &goal, long long *ev, double *dmg, long long live) const {
         int rj = -1;
         goal = 0;
         {
@@ -622,26 +667,9 @@ struct LaneGame {
         return rj;
     }
 
-    // ---- one game-step (GameSim::updateSim :126-171); SP/CMD hold the state and the commands ----
-    // returns the event-loop counter of the step (1 when nothing happened)
-    RGS_DEV int step(double &sa, double &sb, long long *ev, double *dmg, long long live) const {
-        Bits<4 * E> wb;
-        Bits<NPAIR> pb;
-        wb.clear();
-        pb.clear();
-#pragma unroll 1
-        for (int e = 0; e < E; ++e) {
-            s.I(S::CS + e) = 0;
-            s.I(S::FL + e) = 0;
-            s.F(S::OFF + 4 * e) = T(0); s.F(S::OFF + 4 * e + 1) = T(0); s.F(S::OFF + 4 * e + 2) = T(0); s.F(S::OFF + 4 * e + 3) = T(0);
-            update_bbox(e);
-            flag_walls(e, wb);
-        }
-#pragma unroll 1
-        for (int a = 0; a < E - 1; ++a)
-#pragma unroll 1
-            for (int b = a + 1; b < E; ++b)
-                if (flag_pair(a, b)) pb.set(pair_index(a, b));
+    // ---- the event loop of one game-step (GameSim::updateSim :136-150) on the flagged items ----
+    // returns the loop counter of the step
+    RGS_DEV int event_loop(Bits<4 * E> &wb, Bits<NPAIR> &pb, double &sa, double &sb, long long *ev, double *dmg, long long live) const {
         int counter = 1;
         if (wb.any() || pb.any()) {
             unsigned qmask = 0, fmask = 0, owners = (1u << E) - 1u;
@@ -693,6 +721,31 @@ struct LaneGame {
             }
             if (qmask != 0) ev[RGS_EV_COUNTER_LIMIT]++;
         }
+        return counter;
+    }
+
+    // ---- one game-step with the state held in shared memory (SP/CMD hold the state and the commands;
+    // teams of more than 3, where the register form below would spill) ----
+    // returns the event-loop counter of the step (1 when nothing happened)
+    RGS_DEV int step(double &sa, double &sb, long long *ev, double *dmg, long long live) const {
+        Bits<4 * E> wb;
+        Bits<NPAIR> pb;
+        wb.clear();
+        pb.clear();
+#pragma unroll 1
+        for (int e = 0; e < E; ++e) {
+            s.I(S::CS + e) = 0;
+            s.I(S::FL + e) = 0;
+            s.F(S::OFF + 4 * e) = T(0); s.F(S::OFF + 4 * e + 1) = T(0); s.F(S::OFF + 4 * e + 2) = T(0); s.F(S::OFF + 4 * e + 3) = T(0);
+            update_bbox(e);
+            flag_walls(e, wb);
+        }
+#pragma unroll 1
+        for (int a = 0; a < E - 1; ++a)
+#pragma unroll 1
+            for (int b = a + 1; b < E; ++b)
+                if (flag_pair(a, b)) pb.set(pair_index(a, b));
+        const int counter = event_loop(wb, pb, sa, sb, ev, dmg, live);
         // commit column 50 (:153-157)
 #pragma unroll 1
         for (int e = 0; e < E; ++e) {
@@ -700,6 +753,105 @@ struct LaneGame {
             eval(e, kGrid, px, py, vx, vy);
             s.F(S::SP + 4 * e) = px; s.F(S::SP + 4 * e + 1) = py; s.F(S::SP + 4 * e + 2) = vx; s.F(S::SP + 4 * e + 3) = vy;
         }
+        return counter;
+    }
+
+    // ---- the same step with the state in REGISTERS (st[4e+c], cmd[2p+a]; compile-time indices only):
+    // a contact-free step (69 % of the S0 steps) never touches shared memory ----
+    // bounding intervals + broad-phase flags of the whole-step segments: update_bbox / flag_walls /
+    // flag_pair with cs = 0 and no offsets, same arithmetic
+    RGS_DEV void head_flags(const T *st, const T *cmd, T *bb, Bits<4 * E> &wb, Bits<NPAIR> &pb) const {
+        const T trem = P.d.dt_col * T(kGrid);
+        const T sl = Slack<T>::v;
+        wb.clear();
+        pb.clear();
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+            const int ty = (e == PK);
+            const T gE = tab->e[ty][kGrid].g;
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                const T p = st[4 * e + a], v = st[4 * e + 2 + a], u = e == PK ? T(0) : cmd[2 * (e == PK ? 0 : e) + a];
+                const T vE = fm(v - u, gE, u);
+                bb[4 * e + 2 * a] = p + tmin(T(0), tmin(v, vE) * trem) + T(0);
+                bb[4 * e + 2 * a + 1] = p + tmax(T(0), tmax(v, vE) * trem) + T(0);
+            }
+            const T lx = P.lim_x[ty] - sl, ly = P.lim_y[ty] - sl;
+            if (bb[4 * e + 3] >= ly) wb.set(4 * e + WALL_UP);
+            if (bb[4 * e + 2] <= -ly) wb.set(4 * e + WALL_DOWN);
+            if (bb[4 * e + 1] >= lx) wb.set(4 * e + WALL_RIGHT);
+            if (bb[4 * e + 0] <= -lx) wb.set(4 * e + WALL_LEFT);
+        }
+#pragma unroll
+        for (int a = 0; a < E - 1; ++a)
+#pragma unroll
+            for (int b = a + 1; b < E; ++b) {
+                const T gx = tmax(T(0), tmax(bb[4 * a] - bb[4 * b + 1], bb[4 * b] - bb[4 * a + 1]));
+                const T gy = tmax(T(0), tmax(bb[4 * a + 2] - bb[4 * b + 3], bb[4 * b + 2] - bb[4 * a + 3]));
+                const T sg = P.d.sig[a == PK][b == PK] + sl;
+                if (fm(gx, gx, gy * gy) <= sg * sg) pb.set(pair_index(a, b));
+            }
+    }
+    // closed-form commit of column 50 of a contact-free step (eval() with j = 50 and zero offsets)
+    RGS_DEV void quiet_commit(T *st, const T *cmd) const {
+        const T tj = P.d.dt_col * T(kGrid);
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+            const LaneGK<T> gk = tab->e[e == PK][kGrid];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) {
+                const T u = e == PK ? T(0) : cmd[2 * (e == PK ? 0 : e) + a];
+                const T w = st[4 * e + 2 + a] - u;
+                st[4 * e + a] = fm(w, gk.k, fm(u, tj, st[4 * e + a])) + T(0);
+                st[4 * e + 2 + a] = fm(w, gk.g, u);
+            }
+        }
+    }
+    // registers -> scratch record at the start of a step that has flagged items
+    RGS_DEV void spill(const T *st, const T *cmd, const T *bb) const {
+#pragma unroll
+        for (int e = 0; e < E; ++e) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                s.F(S::SP + 4 * e + c) = st[4 * e + c];
+                s.F(S::PRV + 4 * e + c) = st[4 * e + c];
+                s.F(S::OFF + 4 * e + c) = T(0);
+                s.F(S::BB + 4 * e + c) = bb[4 * e + c];
+            }
+            s.F(S::CMD + 2 * e) = e == PK ? T(0) : cmd[2 * (e == PK ? 0 : e)];
+            s.F(S::CMD + 2 * e + 1) = e == PK ? T(0) : cmd[2 * (e == PK ? 0 : e) + 1];
+            s.I(S::CS + e) = 0;
+            s.I(S::FL + e) = 0;
+        }
+    }
+    // column 50 of every body -> registers (:153-157)
+    RGS_DEV void commit_to(T *st) const {
+#ifdef RGS_COMMIT_LOOP
+#pragma unroll 1
+        for (int e = 0; e < E; ++e) {  // one copy of eval(): through the record, then into registers
+            T px, py, vx, vy;
+            eval(e, kGrid, px, py, vx, vy);
+            s.F(S::SP + 4 * e) = px; s.F(S::SP + 4 * e + 1) = py; s.F(S::SP + 4 * e + 2) = vx; s.F(S::SP + 4 * e + 3) = vy;
+        }
+#pragma unroll
+        for (int c = 0; c < 4 * E; ++c) st[c] = s.F(S::SP + c);
+#else
+#pragma unroll
+        for (int e = 0; e < E; ++e) eval(e, kGrid, st[4 * e], st[4 * e + 1], st[4 * e + 2], st[4 * e + 3]);
+#endif
+    }
+    RGS_DEV int step_regs(T *st, const T *cmd, double &sa, double &sb, long long *ev, double *dmg, long long live) const {
+        T bb[4 * E];
+        Bits<4 * E> wb;
+        Bits<NPAIR> pb;
+        head_flags(st, cmd, bb, wb, pb);
+        if (!(wb.any() || pb.any())) {
+            quiet_commit(st, cmd);
+            return 1;
+        }
+        spill(st, cmd, bb);
+        const int counter = event_loop(wb, pb, sa, sb, ev, dmg, live);
+        commit_to(st);
         return counter;
     }
 };
@@ -724,25 +876,46 @@ RGS_DEV void write_traj_lane(const RunArgs &A, const LaneScratch<T, NT> &s, int6
     for (int d = 0; d < NP * NP; ++d) rec[1 + SREC + d] = A.damage[game * (NP * NP) + d];
 }
 
-// all n_steps of ONE game (the body of a lane)
+// all n_steps of ONE game (the body of a lane).  Teams of up to 3: the state lives in registers
+// between steps (step_regs); larger teams keep it in the scratch record (step).
 template <typename T, int NT>
 RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const LaneTab<T> *tab, const LaneScratch<T, NT> &s,
                                int64_t game) {
     constexpr int E = 2 * NT + 1, PK = 2 * NT, SREC = 2 + 4 * E, NP = 2 * NT;
+    // Measured on B200 (profiles/r01_ab_variants.md): the register form executes 11 % fewer instructions but its
+    // unrolled code (4576 vs 3440 SASS instructions) misses the instruction cache more (no_instruction stall 5.2
+    // vs 2.3 per issue): 1.82e9 vs 2.16e9 game-steps/s.  It stays available for the phased kernel and for A/B.
+#ifdef RGS_LANE_REG_STATE
+    constexpr bool kRegs = NT <= 3;
+#else
+    constexpr bool kRegs = false;
+#endif
     using S = LaneScratch<T, NT>;
     const LaneGame<T, NT> G(P, tab, s);
     double *srec = A.state + game * SREC;
-#pragma unroll 1
-    for (int slot = 0; slot < E; ++slot) {
-        const int e = slot == 0 ? PK : slot - 1;
+    T st[kRegs ? 4 * E : 1], cmd[kRegs ? 2 * NP : 1];
+    if constexpr (kRegs) {
 #pragma unroll
-        for (int c = 0; c < 4; ++c) {
-            const T v = T(srec[2 + 4 * slot + c]);
-            s.F(S::SP + 4 * e + c) = v;
-            s.F(S::PRV + 4 * e + c) = v;
+        for (int slot = 0; slot < E; ++slot) {
+            const int e = slot == 0 ? PK : slot - 1;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) st[4 * e + c] = T(srec[2 + 4 * slot + c]);
         }
-        s.F(S::CMD + 2 * e) = T(0);
-        s.F(S::CMD + 2 * e + 1) = T(0);
+#pragma unroll
+        for (int c = 0; c < 2 * NP; ++c) cmd[c] = T(0);
+    } else {
+#pragma unroll 1
+        for (int slot = 0; slot < E; ++slot) {
+            const int e = slot == 0 ? PK : slot - 1;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                const T v = T(srec[2 + 4 * slot + c]);
+                s.F(S::SP + 4 * e + c) = v;
+                s.F(S::PRV + 4 * e + c) = v;
+            }
+            s.F(S::CMD + 2 * e) = T(0);
+            s.F(S::CMD + 2 * e + 1) = T(0);
+        }
     }
     double sa = srec[0], sb = srec[1];
     double t_clock = A.clock[game];
@@ -757,37 +930,54 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
     bool fetch = true;
     const bool logging = A.traj != nullptr && A.log_stride > 0;
     int64_t k = 0, log_left = A.log_stride;
+    auto log_now = [&](int64_t kk) {
+        if constexpr (kRegs) {
+#pragma unroll
+            for (int e = 0; e < E; ++e)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) s.F(S::SP + 4 * e + c) = st[4 * e + c];
+        }
+        write_traj_lane<T, NT>(A, s, game, kk, t_clock, sa, sb);
+    };
 #pragma unroll 1
     for (; k < A.n_steps; ++k) {
         if (!(sa < wsc && sb < wsc)) break;  // undecided(), :57-60
         if (fetch) {
             const int64_t ai = (A.synth || aidx < A.n_act) ? aidx : A.n_act - 1;
+            if constexpr (kRegs) {
+#pragma unroll
+                for (int c = 0; c < 2 * NP; ++c)
+                    cmd[c] = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
+                                     : actions[game * A.act_game_stride + ai * (2 * NP) + c];
+            } else {
 #pragma unroll 1
-            for (int c = 0; c < 2 * NP; ++c)
-                s.F(S::CMD + c) = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
-                                          : actions[game * A.act_game_stride + ai * (2 * NP) + c];
+                for (int c = 0; c < 2 * NP; ++c)
+                    s.F(S::CMD + c) = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
+                                              : actions[game * A.act_game_stride + ai * (2 * NP) + c];
+            }
             fetch = false;
         }
         if (++phase == A.hold) { phase = 0; ++aidx; fetch = true; }
-        loop_iters += G.step(sa, sb, gev, dmg, live);
+        if constexpr (kRegs) loop_iters += G.step_regs(st, cmd, sa, sb, gev, dmg, live);
+        else loop_iters += G.step(sa, sb, gev, dmg, live);
         t_clock += (double)P.d.dt;  // t_ += dt_ (:158), fp64 like the reference clock
         ++live;
         if (decided == 0 && !(sa < wsc && sb < wsc)) decided = live;
         if (logging && --log_left == 0) {
             log_left = A.log_stride;
-            write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb);
+            log_now(k);
         }
     }
     if (logging)  // frozen steps of a decided game (GameSim::run :121-123) repeat the frozen state
         for (; k < A.n_steps; ++k)
-            if (--log_left == 0) { log_left = A.log_stride; write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb); }
+            if (--log_left == 0) { log_left = A.log_stride; log_now(k); }
     srec[0] = sa;
     srec[1] = sb;
-#pragma unroll 1
+#pragma unroll
     for (int slot = 0; slot < E; ++slot) {
         const int e = slot == 0 ? PK : slot - 1;
 #pragma unroll
-        for (int c = 0; c < 4; ++c) srec[2 + 4 * slot + c] = (double)s.F(S::SP + 4 * e + c);
+        for (int c = 0; c < 4; ++c) srec[2 + 4 * slot + c] = kRegs ? (double)st[kRegs ? 4 * e + c : 0] : (double)s.F(S::SP + 4 * e + c);
     }
     A.clock[game] = t_clock;
     gev[RGS_EV_LIVE_STEPS] = live;

@@ -55,13 +55,17 @@ template <typename T>
 static cudaError_t launch_lane(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count) {
     const FastParams<T> P = make_fast_params<T>(p);
     switch (n_team) {
+#ifndef RGS_EXP_ONLY_2V2
     case 1: return launch_lane_nt<T, 1>(P, A, stream, sm_count);
+#endif
     case 2: return launch_lane_nt<T, 2>(P, A, stream, sm_count);
+#ifndef RGS_EXP_ONLY_2V2
     case 3: return launch_lane_nt<T, 3>(P, A, stream, sm_count);
     case 4: return launch_lane_nt<T, 4>(P, A, stream, sm_count);
     case 5: return launch_lane_nt<T, 5>(P, A, stream, sm_count);
     case 6: return launch_lane_nt<T, 6>(P, A, stream, sm_count);
     case 7: return launch_lane_nt<T, 7>(P, A, stream, sm_count);
+#endif
     default: return cudaErrorInvalidValue;
     }
 }

@@ -149,14 +149,14 @@ struct PhaseKernel {
             }
         }
     }
-    RGS_DEV void do_wall_item(int item) const {
+    RGS_DEV_BIG void do_wall_item(int item) const {
         const int r = item & 1023, a = (item >> 10) & 15, wk = (item >> 14) & 15, base = (item >> 18) & 63;
         const Game G(P, sh.tab, sh.rec(r));
         T t;
         const int c = G.search_wall(a, wk, base, t);
         if (c <= kGrid) fold_locked(G, a, c, t, wk, 15);
     }
-    RGS_DEV void do_pair_item(int item) const {
+    RGS_DEV_BIG void do_pair_item(int item) const {
         const int r = item & 1023, a = (item >> 10) & 15, b = (item >> 14) & 15, base = (item >> 18) & 63;
         const Game G(P, sh.tab, sh.rec(r));
         T t;
@@ -290,54 +290,14 @@ struct PhaseKernel {
                                     : actions[ts.game * A.act_game_stride + ai * (2 * NP) + c];
             ts.fetch = false;
         }
-        // bounding intervals of the whole-step segments (LaneGame::update_bbox with cs = 0, no offsets)
+        // bounding intervals + broad-phase flags in registers; a contact-free step ends here
+        const Game G0(P, sh.tab, sh.rec(0));  // the register helpers touch no record
         T bb[4 * E];
-        const T trem = P.d.dt_col * T(kGrid);
         Bits<4 * E> wb;
         Bits<NPAIR> pb;
-        wb.clear();
-        pb.clear();
-        const T sl = Slack<T>::v;
-#pragma unroll
-        for (int e = 0; e < E; ++e) {
-            const int ty = (e == PK);
-            const T gE = sh.tab->e[ty][kGrid].g;
-#pragma unroll
-            for (int a = 0; a < 2; ++a) {
-                const T p = ts.st[4 * e + a], v = ts.st[4 * e + 2 + a], u = e == PK ? T(0) : ts.cmd[2 * (e == PK ? 0 : e) + a];
-                const T vE = fm(v - u, gE, u);
-                bb[4 * e + 2 * a] = p + tmin(T(0), tmin(v, vE) * trem) + T(0);
-                bb[4 * e + 2 * a + 1] = p + tmax(T(0), tmax(v, vE) * trem) + T(0);
-            }
-            const T lx = P.lim_x[ty] - sl, ly = P.lim_y[ty] - sl;  // LaneGame::flag_walls
-            if (bb[4 * e + 3] >= ly) wb.set(4 * e + WALL_UP);
-            if (bb[4 * e + 2] <= -ly) wb.set(4 * e + WALL_DOWN);
-            if (bb[4 * e + 1] >= lx) wb.set(4 * e + WALL_RIGHT);
-            if (bb[4 * e + 0] <= -lx) wb.set(4 * e + WALL_LEFT);
-        }
-#pragma unroll
-        for (int a = 0; a < E - 1; ++a)
-#pragma unroll
-            for (int b = a + 1; b < E; ++b) {  // LaneGame::flag_pair
-                const T gx = tmax(T(0), tmax(bb[4 * a] - bb[4 * b + 1], bb[4 * b] - bb[4 * a + 1]));
-                const T gy = tmax(T(0), tmax(bb[4 * a + 2] - bb[4 * b + 3], bb[4 * b + 2] - bb[4 * a + 3]));
-                const T sg = P.d.sig[a == PK][b == PK] + sl;
-                if (fm(gx, gx, gy * gy) <= sg * sg) pb.set(Game::pair_index(a, b));
-            }
+        G0.head_flags(ts.st, ts.cmd, bb, wb, pb);
         if (!(wb.any() || pb.any())) {
-            // closed-form commit of column 50 (LaneGame::eval with j = 50, zero offsets)
-            const T tj = P.d.dt_col * T(kGrid);
-#pragma unroll
-            for (int e = 0; e < E; ++e) {
-                const LaneGK<T> gk = sh.tab->e[e == PK][kGrid];
-#pragma unroll
-                for (int a = 0; a < 2; ++a) {
-                    const T u = e == PK ? T(0) : ts.cmd[2 * (e == PK ? 0 : e) + a];
-                    const T w = ts.st[4 * e + 2 + a] - u;
-                    ts.st[4 * e + a] = fm(w, gk.k, fm(u, tj, ts.st[4 * e + a])) + T(0);
-                    ts.st[4 * e + 2 + a] = fm(w, gk.g, u);
-                }
-            }
+            G0.quiet_commit(ts.st, ts.cmd);
             finish_step(ts, 1);
             return;
         }
@@ -346,20 +306,7 @@ struct PhaseKernel {
         ts.held = -1;
         ts.rec = r;
         const S s = sh.rec(r);
-#pragma unroll
-        for (int e = 0; e < E; ++e) {
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                s.F(S::SP + 4 * e + c) = ts.st[4 * e + c];
-                s.F(S::PRV + 4 * e + c) = ts.st[4 * e + c];
-                s.F(S::OFF + 4 * e + c) = T(0);
-                s.F(S::BB + 4 * e + c) = bb[4 * e + c];
-            }
-            s.F(S::CMD + 2 * e) = e == PK ? T(0) : ts.cmd[2 * (e == PK ? 0 : e)];
-            s.F(S::CMD + 2 * e + 1) = e == PK ? T(0) : ts.cmd[2 * (e == PK ? 0 : e) + 1];
-            s.I(S::CS + e) = 0;
-            s.I(S::FL + e) = 0;
-        }
+        Game(P, sh.tab, s).spill(ts.st, ts.cmd, bb);
         s.I(R::QMASK) = 0;
         s.I(R::SEQ) = 0;
         s.I(R::BASE) = 1;
@@ -475,7 +422,7 @@ struct PhaseKernel {
 
     // ---- RESOLVE (thread = popped event).  When the re-scan flags nothing the same thread goes on
     // with the queue (next event, or end of step: three steps out of four with a contact end here) ----
-    RGS_DEV void resolve_record(int r) const {
+    RGS_DEV_BIG void resolve_record(int r) const {
         const S s = sh.rec(r);
         const Game G(P, sh.tab, s);
         const int64_t game = s.I(R::GAME);

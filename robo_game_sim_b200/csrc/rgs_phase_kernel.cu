@@ -80,9 +80,13 @@ template <typename T>
 static cudaError_t launch_phase(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count) {
     const FastParams<T> P = make_fast_params<T>(p);
     switch (n_team) {
+#ifndef RGS_EXP_ONLY_2V2
     case 1: return launch_phase_nt<T, 1>(P, A, stream, sm_count);
+#endif
     case 2: return launch_phase_nt<T, 2>(P, A, stream, sm_count);
+#ifndef RGS_EXP_ONLY_2V2
     case 3: return launch_phase_nt<T, 3>(P, A, stream, sm_count);
+#endif
     default: return cudaErrorInvalidValue;  // larger teams run the one-lane-per-game kernel
     }
 }

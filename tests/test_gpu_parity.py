@@ -218,7 +218,7 @@ def test_fast64_tracks_oracle(rgs):
 
 
 def test_phase_kernel_equals_lane_kernel_on_gpu(rgs, monkeypatch):
-    """The block-compacted K2 (default) and the one-lane-per-game K2 (RGS_K2_LANE=1) give the same bits
+    """The block-compacted K2 (RGS_K2_LANE=0) and the one-lane-per-game K2 (default) give the same bits
     for every game of a 300k-game batch, fp32 and fp64, with trajectory logging and on-chip commands."""
     for mode, n, steps in (("fast", 300_000, 100), ("fast64", 60_000, 60)):
         outs = []
