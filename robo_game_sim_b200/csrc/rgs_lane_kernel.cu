@@ -4,6 +4,8 @@
 // Shared memory per CTA: the closed-form coefficient table + one scratch record per thread, laid
 // out word-major ([word][thread]) so that the run-time body indices of the event path never cause
 // a bank conflict (bank = lane) and never force per-thread arrays into local memory.
+#include <cstdlib>
+
 #include "rgs_lane.cuh"
 #include "rgs_host_params.h"
 #include "rgs_kernels.h"
@@ -35,7 +37,10 @@ static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cuda
     using S = LaneScratch<T, NT>;
     constexpr int kThreads = 64;
     constexpr size_t tab_bytes = (sizeof(LaneTab<T>) + 15) & ~size_t(15);
-    const size_t smem = tab_bytes + ((size_t)S::NF * sizeof(T) + (size_t)S::NI * sizeof(int)) * kThreads;
+    size_t smem = tab_bytes + ((size_t)S::NF * sizeof(T) + (size_t)S::NI * sizeof(int)) * kThreads;
+#ifdef RGS_EXP_ONLY_2V2
+    if (const char *pad = std::getenv("RGS_EXP_SMEM_PAD")) smem += (size_t)std::atoi(pad);  // occupancy sensitivity experiments
+#endif
     auto kern = rollout_lane_kernel<T, NT, kThreads>;
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
