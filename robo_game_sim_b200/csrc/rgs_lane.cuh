@@ -133,6 +133,20 @@ template <typename T>
 RGS_DEV T tmax(T a, T b) { return a > b ? a : b; }
 #endif
 
+// square root used ONLY to decide how many columns a search may skip (conservative advancement keeps a 2 %
+// margin, so one MUFU.SQRT is enough there; times of impact and overlaps use the IEEE sqrt)
+#if !defined(RGS_HOST_EMU) && !defined(RGS_NO_APPROX_SKIP_SQRT)
+RGS_DEV float skip_sqrt(float x) {
+    float r;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+RGS_DEV double skip_sqrt(double x) { return sqrt(x); }
+#else
+template <typename T>
+RGS_DEV T skip_sqrt(T x) { return T(sqrt(x)); }
+#endif
+
 // broad-phase slack: the bounding intervals are evaluated with different roundings than the
 // column positions, so thresholds are inflated by a few hundred ulps of the arena size
 template <typename T> struct Slack;
@@ -370,7 +384,7 @@ struct LaneGame {
             }
             const T S2 = fm(sx, sx, sy * sy);
             const bool jump = s.I(S::FL + a) > base || s.I(S::FL + b) > base;
-            inv_sh = jump ? T(0) : T(0.98) / (T(sqrt(S2)) * h + T(1.0e-12));
+            inv_sh = jump ? T(0) : T(0.98) / (skip_sqrt(S2) * h + T(1.0e-12));
         }
         int c = base;
         const PosSeg ga = pos_seg(a), gb = pos_seg(b);
@@ -393,7 +407,7 @@ struct LaneGame {
                 }
                 ++c;
             } else {
-                const T skip = (T(sqrt(ssq)) - sigma) * inv_sh;
+                const T skip = (skip_sqrt(ssq) - sigma) * inv_sh;
                 c += 1 + (int)tmin(skip, T(64));
             }
         }
@@ -501,7 +515,7 @@ struct LaneGame {
                 const T va1 = fm(va0 - ua, tab->e[tyi][rem].g, ua), vb1 = fm(vb0 - ub, tab->e[tyj][rem].g, ub);
                 sy = tmax(tmax(va0, va1) - tmin(vb0, vb1), tmax(vb0, vb1) - tmin(va0, va1));
             }
-            inv_sh = T(0.98) / (T(sqrt(fm(sx, sx, sy * sy))) * P.d.dt_col + T(1.0e-12));
+            inv_sh = T(0.98) / (skip_sqrt(fm(sx, sx, sy * sy)) * P.d.dt_col + T(1.0e-12));
         }
         int c = base + 1;
         PosSeg gi = pos_seg(bi), gj = pos_seg(bj);
@@ -529,7 +543,7 @@ struct LaneGame {
                 ev[RGS_EV_OVERLAP_FIXES]++;
                 ++c;
             } else {
-                const T skip = (T(sqrt(ssq)) - sigma) * inv_sh;
+                const T skip = (skip_sqrt(ssq) - sigma) * inv_sh;
                 c += 1 + (int)tmin(skip, T(64));
             }
         }
@@ -741,19 +755,47 @@ struct LaneGame {
         Bits<NPAIR> pb;
         wb.clear();
         pb.clear();
+        {   // whole-step segments: update_bbox + flag_walls with cs = 0 and zero offsets, from registers
+            const T trem = P.d.dt_col * T(kGrid), sl = Slack<T>::v;
+            const T gE[2] = {tab->e[0][kGrid].g, tab->e[1][kGrid].g};
 #pragma unroll 1
-        for (int e = 0; e < E; ++e) {
-            s.I(S::CS + e) = 0;
-            s.I(S::FL + e) = 0;
-            s.F(S::OFF + 4 * e) = T(0); s.F(S::OFF + 4 * e + 1) = T(0); s.F(S::OFF + 4 * e + 2) = T(0); s.F(S::OFF + 4 * e + 3) = T(0);
-            update_bbox(e);
-            flag_walls(e, wb);
+            for (int e = 0; e < E; ++e) {
+                const int ty = (e == PK);
+                s.I(S::CS + e) = 0;
+                s.I(S::FL + e) = 0;
+                T lohi[4];
+#pragma unroll
+                for (int a = 0; a < 2; ++a) {
+                    s.F(S::OFF + 4 * e + a) = T(0);
+                    s.F(S::OFF + 4 * e + 2 + a) = T(0);
+                    const T p = s.F(S::SP + 4 * e + a), v = s.F(S::SP + 4 * e + 2 + a), u = s.F(S::CMD + 2 * e + a);
+                    const T vE = fm(v - u, gE[ty], u);
+                    lohi[2 * a] = p + tmin(T(0), tmin(v, vE) * trem) + T(0);
+                    lohi[2 * a + 1] = p + tmax(T(0), tmax(v, vE) * trem) + T(0);
+                    s.F(S::BB + 4 * e + 2 * a) = lohi[2 * a];
+                    s.F(S::BB + 4 * e + 2 * a + 1) = lohi[2 * a + 1];
+                }
+                const T lx = P.lim_x[ty] - sl, ly = P.lim_y[ty] - sl;
+                if (lohi[3] >= ly) wb.set(4 * e + WALL_UP);
+                if (lohi[2] <= -ly) wb.set(4 * e + WALL_DOWN);
+                if (lohi[1] >= lx) wb.set(4 * e + WALL_RIGHT);
+                if (lohi[0] <= -lx) wb.set(4 * e + WALL_LEFT);
+            }
+            // flag_pair with the first body's interval held in registers
+            const T sgpp = P.d.sig[0][0] + sl, sgpk = P.d.sig[0][1] + sl;
+            const T thr_pp = sgpp * sgpp, thr_pk = sgpk * sgpk;
+            int pidx = 0;
+#pragma unroll 1
+            for (int a = 0; a < E - 1; ++a) {
+                const T alx = s.F(S::BB + 4 * a), ahx = s.F(S::BB + 4 * a + 1), aly = s.F(S::BB + 4 * a + 2), ahy = s.F(S::BB + 4 * a + 3);
+#pragma unroll 1
+                for (int b = a + 1; b < E; ++b, ++pidx) {
+                    const T gx = tmax(T(0), tmax(alx - s.F(S::BB + 4 * b + 1), s.F(S::BB + 4 * b) - ahx));
+                    const T gy = tmax(T(0), tmax(aly - s.F(S::BB + 4 * b + 3), s.F(S::BB + 4 * b + 2) - ahy));
+                    if (fm(gx, gx, gy * gy) <= (b == PK ? thr_pk : thr_pp)) pb.set(pidx);
+                }
+            }
         }
-#pragma unroll 1
-        for (int a = 0; a < E - 1; ++a)
-#pragma unroll 1
-            for (int b = a + 1; b < E; ++b)
-                if (flag_pair(a, b)) pb.set(pair_index(a, b));
         const int counter = event_loop(wb, pb, sa, sb, ev, dmg, live);
         // commit column 50 (:153-157)
 #pragma unroll 1
@@ -954,10 +996,14 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
         if (fetch) {
             const int64_t ai = (A.synth || aidx < A.n_act) ? aidx : A.n_act - 1;
             if constexpr (kRegs) {
+#pragma unroll 1
+                for (int c = 0; c < 2 * NP; ++c) {  // one copy of the generator; the select chain keeps cmd[] in registers
+                    const T v = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
+                                        : actions[game * A.act_game_stride + ai * (2 * NP) + c];
 #pragma unroll
-                for (int c = 0; c < 2 * NP; ++c)
-                    cmd[c] = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
-                                     : actions[game * A.act_game_stride + ai * (2 * NP) + c];
+                    for (int c2 = 0; c2 < 2 * NP; ++c2)
+                        if (c2 == c) cmd[c2] = v;
+                }
             } else {
 #pragma unroll 1
                 for (int c = 0; c < 2 * NP; ++c)
