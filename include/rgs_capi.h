@@ -115,6 +115,22 @@ int rgs_batch_run(rgs_batch *b, const void *d_actions, int64_t n_act, int64_t ho
 int rgs_batch_run_synth(rgs_batch *b, uint64_t seed, int64_t first_game, int64_t step0, int64_t hold, double u_max,
                         int64_t n_steps, int64_t log_stride, double *d_traj, void *stream);
 
+/* K3, shared-state rollout sampling (BASELINE configs[4]: 4096 candidate command sequences x 50 steps from one
+ * state per controller tick).  It takes over the ROLE of the reference's per-tick trajectory optimisation
+ * (DMPC.compute_control, reference py/src/DMPC.py:16-54: direct collocation over an internal linear model,
+ * SNOPT), not its algorithm: candidates are rolled out through the real GameSim step instead.
+ *   rgs_batch_reset_shared: every game of the batch starts from the ONE state record d_state [2+4E]
+ *                           (clock, damage and event records zeroed);
+ *   rgs_batch_run:          candidate g follows its own command records (act_game_stride != 0);
+ *   rgs_batch_terminal_cost: d_cost[g] = sum_{p,c} w[p][c] (x_g[p][c] - x_des[p][c])^2 over the 2n players
+ *                           (d_x_des, d_weights: [2n,4] doubles; the reference's terminal weight is
+ *                           Omega_N_max = diag(10,10,20,20), py/src/DMPCTeam.py:56-59; weight 0 leaves a
+ *                           player out), d_best[0] = arg-min (lowest index on ties), d_best[1] = the
+ *                           minimum cost as double bits. */
+int rgs_batch_reset_shared(rgs_batch *b, const double *d_state, void *stream);
+int rgs_batch_terminal_cost(rgs_batch *b, const double *d_x_des, const double *d_weights, double *d_cost, int64_t *d_best,
+                            void *stream);
+
 /* State / clock / damage / events of all games into caller-provided DEVICE buffers (any may be NULL). */
 int rgs_batch_get(rgs_batch *b, double *d_state, double *d_t, double *d_damage, int64_t *d_events, void *stream);
 

@@ -10,3 +10,4 @@ CPU implementation: importing is cheap, but the first compute call needs the bui
 from ._capi import MODE_EXACT_F64, MODE_FAST_F32, MODE_FAST_F64, EV_NAMES, launch_count  # noqa: F401
 from .gamesim import BatchedGameSim, GameSim, synth_inputs  # noqa: F401
 from .montecarlo import monte_carlo_batched, reduce_stats, stats_to_dict  # noqa: F401
+from . import sampler  # noqa: F401,E402  (shared-state rollout sampling, BASELINE configs[4])

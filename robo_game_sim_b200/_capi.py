@@ -44,6 +44,8 @@ SIGNATURES = {
     "rgs_batch_run_synth": (C.c_int, [_vp, _u64, _i64, _i64, _i64, _dbl, _i64, _i64, _vp, _vp]),
     "rgs_batch_get": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "rgs_batch_stats": (C.c_int, [_vp, _vp, _vp]),
+    "rgs_batch_reset_shared": (C.c_int, [_vp, _vp, _vp]),
+    "rgs_batch_terminal_cost": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "rgs_synth_inputs": (C.c_int, [C.c_int, _u64, _i64, _i64, _i32, _i64, _dbl, _vp, _vp, _i32, _vp]),
     "rgs_measure_peak": (C.c_int, [C.c_int, _i32, C.POINTER(_dbl)]),
     "rgs_batch_run_host": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),

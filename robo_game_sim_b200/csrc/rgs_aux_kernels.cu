@@ -15,7 +15,7 @@ struct ResetArgs {
 
 __global__ void __launch_bounds__(256) reset_kernel(const __grid_constant__ ResetArgs R, int64_t n_games,
                                                     const double *__restrict__ x0_ball, int64_t x0_stride,
-                                                    const double *__restrict__ state0, double *__restrict__ state,
+                                                    const double *__restrict__ state0, int64_t state0_stride, double *__restrict__ state,
                                                     double *__restrict__ clock, double *__restrict__ damage,
                                                     long long *__restrict__ events) {
     const int E = 2 * R.n_team + 1, SREC = 2 + 4 * E, NP = 2 * R.n_team, DREC = NP * NP;
@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(256) reset_kernel(const __grid_constant__ Rese
         const int64_t g = w / SREC;
         const int idx = (int)(w - g * SREC);
         double v;
-        if (state0) v = state0[w];
+        if (state0) v = state0[g * state0_stride + idx];
         else if (idx < 2) v = 0.0;
         else if (idx < 6) v = x0_ball ? x0_ball[g * x0_stride + (idx - 2)] : 0.0;
         else {
@@ -41,8 +41,8 @@ __global__ void __launch_bounds__(256) reset_kernel(const __grid_constant__ Rese
 }
 
 cudaError_t launch_reset(int n_team, int64_t n_games, const rgs_params &p, const double *d_x0_ball, int64_t x0_stride,
-                         const double *d_state0, double *state, double *clock, double *damage, long long *events,
-                         cudaStream_t stream) {
+                         const double *d_state0, int64_t state0_stride, double *state, double *clock, double *damage,
+                         long long *events, cudaStream_t stream) {
     ResetArgs R;
     R.n_team = n_team;
     for (int team = 0; team < 2; ++team)
@@ -57,8 +57,77 @@ cudaError_t launch_reset(int n_team, int64_t n_games, const rgs_params &p, const
     int64_t blocks = (n_games * (2 + 4 * (2 * n_team + 1)) + threads - 1) / threads;
     if (blocks > 148 * 16) blocks = 148 * 16;
     if (blocks < 1) blocks = 1;
-    reset_kernel<<<(unsigned)blocks, threads, 0, stream>>>(R, n_games, d_x0_ball, x0_stride, d_state0, state, clock,
+    reset_kernel<<<(unsigned)blocks, threads, 0, stream>>>(R, n_games, d_x0_ball, x0_stride, d_state0, state0_stride, state, clock,
                                                            damage, events);
+    return cudaGetLastError();
+}
+
+
+// ---- K3 epilogue: terminal cost of every rolled-out candidate + arg-min ------------------------
+// cost[g] = sum over players p, components c of w[p][c] * (x_g[p][c] - x_des[p][c])^2: the terminal
+// term of the reference's DMPC objective, (x_N - x_des)^T Omega_N (x_N - x_des) with
+// Omega_N_max = diag(10, 10, 20, 20) (reference py/src/DMPCTeam.py:56-59, py/src/DMPC.py:16-54),
+// evaluated on the SIMULATED final state instead of the controller's internal linear model.
+// best[0] = arg-min (lowest index among equal costs), best[1] = its cost (double bits).
+__global__ void __launch_bounds__(256) cost_kernel(int64_t n_games, int srec, int np, const double *__restrict__ state,
+                                                   const double *__restrict__ x_des, const double *__restrict__ w,
+                                                   double *__restrict__ cost, unsigned long long *__restrict__ block_best) {
+    __shared__ double sc[256];
+    __shared__ long long si[256];
+    double bc = 1.0e300;
+    long long bi = -1;
+    for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < n_games; g += (int64_t)gridDim.x * blockDim.x) {
+        const double *x = state + g * srec + 6;  // players follow [TAS, TBS, PK(4)]
+        double c = 0.0;
+        for (int k = 0; k < 4 * np; ++k) {
+            const double d = x[k] - x_des[k];
+            c += w[k] * d * d;
+        }
+        cost[g] = c;
+        if (c < bc) { bc = c; bi = g; }  // g increases: the first minimum of this thread is kept
+    }
+    sc[threadIdx.x] = bc;
+    si[threadIdx.x] = bi;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if (threadIdx.x < o) {
+            const double c2 = sc[threadIdx.x + o];
+            const long long i2 = si[threadIdx.x + o];
+            if (i2 >= 0 && (si[threadIdx.x] < 0 || c2 < sc[threadIdx.x] || (c2 == sc[threadIdx.x] && i2 < si[threadIdx.x]))) {
+                sc[threadIdx.x] = c2;
+                si[threadIdx.x] = i2;
+            }
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        block_best[2 * blockIdx.x] = (unsigned long long)si[0];
+        block_best[2 * blockIdx.x + 1] = (unsigned long long)__double_as_longlong(sc[0]);
+    }
+}
+__global__ void argmin_final_kernel(int n_blocks, const unsigned long long *__restrict__ block_best, long long *__restrict__ best) {
+    double bc = 1.0e300;
+    long long bi = -1;
+    for (int b = 0; b < n_blocks; ++b) {
+        const long long i = (long long)block_best[2 * b];
+        const double c = __longlong_as_double((long long)block_best[2 * b + 1]);
+        if (i >= 0 && (bi < 0 || c < bc || (c == bc && i < bi))) { bc = c; bi = i; }
+    }
+    best[0] = bi;
+    best[1] = __double_as_longlong(bc);
+}
+
+cudaError_t launch_terminal_cost(int n_team, int64_t n_games, const double *state, const double *d_x_des, const double *d_w,
+                                 double *d_cost, unsigned long long *scratch, long long *d_best, cudaStream_t stream) {
+    const int threads = 256;
+    int64_t blocks = (n_games + threads - 1) / threads;
+    if (blocks > kCostBlocks) blocks = kCostBlocks;
+    if (blocks < 1) blocks = 1;
+    cost_kernel<<<(unsigned)blocks, threads, 0, stream>>>(n_games, 2 + 4 * (2 * n_team + 1), 2 * n_team, state, d_x_des, d_w, d_cost,
+                                                          scratch);
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return e;
+    argmin_final_kernel<<<1, 1, 0, stream>>>((int)blocks, scratch, d_best);
     return cudaGetLastError();
 }
 

@@ -73,6 +73,7 @@ struct rgs_batch {
     bool lane_k2 = true;   // RGS_K2_LANE=0: the phased block kernel (rgs_phase.cuh) instead of one lane per game (A/B; teams <= 3)
     double *state = nullptr, *clock = nullptr, *damage = nullptr;
     long long *events = nullptr, *stats = nullptr;
+    unsigned long long *cost_scratch = nullptr;  // K3 arg-min partials, allocated on first use
     // staging for rgs_batch_run_host
     void *stage_actions = nullptr;
     size_t stage_actions_bytes = 0;
@@ -249,6 +250,7 @@ int rgs_batch_destroy(rgs_batch *b) {
     cudaFree(b->damage);
     cudaFree(b->events);
     cudaFree(b->stats);
+    cudaFree(b->cost_scratch);
     cudaFree(b->stage_actions);
     cudaFree(b->stage_x0);
     for (int k = 0; k < 2; ++k) {
@@ -274,10 +276,36 @@ int rgs_batch_reset(rgs_batch *b, const double *d_x0_ball, int64_t x0_stride, co
     if (x0_stride != 0 && x0_stride < 4) return fail(RGS_EINVAL, "x0_stride must be 0 (shared) or >= 4");
     if (b->n_games == 0) return RGS_OK;
     DeviceGuard guard(b->device);
-    cudaError_t e = rgs::launch_reset(b->n_team, b->n_games, b->p, d_x0_ball, x0_stride, d_state0, b->state, b->clock,
+    cudaError_t e = rgs::launch_reset(b->n_team, b->n_games, b->p, d_x0_ball, x0_stride, d_state0, b->srec, b->state, b->clock,
                                       b->damage, b->events, static_cast<cudaStream_t>(stream));
     if (e != cudaSuccess) return cuda_fail(e, "reset kernel launch");
     g_launches.fetch_add(1);
+    return RGS_OK;
+}
+
+int rgs_batch_reset_shared(rgs_batch *b, const double *d_state, void *stream) {
+    if (!b) return fail(RGS_EINVAL, "batch is NULL");
+    if (!d_state) return fail(RGS_EINVAL, "d_state is NULL");
+    if (b->n_games == 0) return RGS_OK;
+    DeviceGuard guard(b->device);
+    cudaError_t e = rgs::launch_reset(b->n_team, b->n_games, b->p, nullptr, 0, d_state, 0, b->state, b->clock, b->damage,
+                                      b->events, static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "reset kernel launch");
+    g_launches.fetch_add(1);
+    return RGS_OK;
+}
+
+int rgs_batch_terminal_cost(rgs_batch *b, const double *d_x_des, const double *d_weights, double *d_cost, int64_t *d_best,
+                            void *stream) {
+    if (!b) return fail(RGS_EINVAL, "batch is NULL");
+    if (!d_x_des || !d_weights || !d_cost || !d_best) return fail(RGS_EINVAL, "d_x_des, d_weights, d_cost and d_best are required");
+    if (b->n_games == 0) return fail(RGS_EINVAL, "empty batch has no minimum");
+    DeviceGuard guard(b->device);
+    if (!b->cost_scratch) RGS_CUDA(cudaMalloc(&b->cost_scratch, 2 * rgs::kCostBlocks * sizeof(unsigned long long)));
+    cudaError_t e = rgs::launch_terminal_cost(b->n_team, b->n_games, b->state, d_x_des, d_weights, d_cost, b->cost_scratch,
+                                              reinterpret_cast<long long *>(d_best), static_cast<cudaStream_t>(stream));
+    if (e != cudaSuccess) return cuda_fail(e, "terminal cost kernel launch");
+    g_launches.fetch_add(2);
     return RGS_OK;
 }
 
@@ -394,7 +422,7 @@ int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_acti
         if (h_x0_ball)
             RGS_CUDA(cudaMemcpyAsync(b->stage_x0 + g0 * 4, h_x0_ball + g0 * 4, (size_t)ng * 4 * sizeof(double),
                                      cudaMemcpyHostToDevice, s));
-        cudaError_t e = rgs::launch_reset(b->n_team, ng, b->p, h_x0_ball ? b->stage_x0 + g0 * 4 : nullptr, 4, nullptr,
+        cudaError_t e = rgs::launch_reset(b->n_team, ng, b->p, h_x0_ball ? b->stage_x0 + g0 * 4 : nullptr, 4, nullptr, 0,
                                           b->state + g0 * b->srec, b->clock + g0, b->damage + g0 * b->dmg_rec,
                                           b->events + g0 * RGS_N_EVENTS, s);
         if (e != cudaSuccess) return cuda_fail(e, "reset kernel launch");

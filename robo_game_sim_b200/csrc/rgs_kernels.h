@@ -32,8 +32,13 @@ cudaError_t launch_stats(int n_team, int64_t n_games, const double *state, const
 
 // K5: batched reset + synthetic S0 inputs (rgs_aux_kernels.cu)
 cudaError_t launch_reset(int n_team, int64_t n_games, const rgs_params &p, const double *d_x0_ball, int64_t x0_stride,
-                         const double *d_state0, double *state, double *clock, double *damage, long long *events,
-                         cudaStream_t stream);
+                         const double *d_state0, int64_t state0_stride, double *state, double *clock, double *damage,
+                         long long *events, cudaStream_t stream);
+
+// K3 epilogue: terminal cost of every candidate + arg-min (rgs_aux_kernels.cu); scratch = 2 * kCostBlocks words
+constexpr int kCostBlocks = 148 * 4;
+cudaError_t launch_terminal_cost(int n_team, int64_t n_games, const double *state, const double *d_x_des, const double *d_w,
+                                 double *d_cost, unsigned long long *scratch, long long *d_best, cudaStream_t stream);
 cudaError_t launch_synth(uint64_t seed, int64_t first_game, int64_t n, int n_team, int64_t n_act, double u_max,
                          double *d_x0_ball, void *d_actions, int dtype, cudaStream_t stream);
 

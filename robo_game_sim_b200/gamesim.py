@@ -255,6 +255,34 @@ class BatchedGameSim:
         _capi.check(self._lib.rgs_batch_stats(self._h, out.data_ptr(), self._stream()))
         return out
 
+    # ---- K3: shared-state rollout sampling ----
+    def reset_shared(self, state):
+        """Every game of the batch starts from the ONE state record `state` [2+4E] (BASELINE configs[4])."""
+        torch = self._torch
+        s0 = self._dev_tensor(state, torch.float64, "state").reshape(-1)
+        if s0.numel() != self.state_size:
+            raise ValueError(f"state must have {self.state_size} elements, got {s0.numel()}")
+        _capi.check(self._lib.rgs_batch_reset_shared(self._h, s0.data_ptr(), self._stream()))
+        self._keep = [s0]
+        return self
+
+    def terminal_cost(self, x_des, weights):
+        """cost[g] = sum_{p,c} weights[p,c] * (x_g[p,c] - x_des[p,c])**2 over the 2n players of every game, and
+        the arg-min.  x_des, weights: [2n,4].  Returns (cost [N] float64 device tensor, best index int, best cost)."""
+        torch = self._torch
+        npl = 2 * self.n_team
+        xd = self._dev_tensor(x_des, torch.float64, "x_des")
+        w = self._dev_tensor(weights, torch.float64, "weights")
+        if xd.numel() != 4 * npl or w.numel() != 4 * npl:
+            raise ValueError(f"x_des and weights must have shape ({npl}, 4)")
+        cost = torch.empty(self.n_games, dtype=torch.float64, device=self.device)
+        best = torch.empty(2, dtype=torch.int64, device=self.device)
+        _capi.check(self._lib.rgs_batch_terminal_cost(self._h, xd.data_ptr(), w.data_ptr(), cost.data_ptr(), best.data_ptr(),
+                                                      self._stream()))
+        self._keep = [xd, w]
+        b = best.cpu()
+        return cost, int(b[0]), float(b[1:2].view(torch.float64)[0])
+
     # ---- host-buffer entry point (end-to-end path) ----
     def run_host(self, x0_ball, actions, n_steps, hold=1, want_state=True, want_events=True, out=None):
         """x0_ball [N,4] float64 and actions [N,n_act,2n,2] (float32 in "fast" mode, else float64)

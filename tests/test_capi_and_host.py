@@ -190,3 +190,32 @@ def test_stats_reduction_world_size_2_gloo(tmp_path):
     outs = [p.communicate(timeout=180)[0] for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0 and "ok" in o, o
+
+
+def test_sampler_targets_follow_the_reference_play_logic():
+    """Host side of the rollout sampler: DMPCTeam.execute's play decision and DMPCPlayer.get_action's
+    x_des (reference py/src/DMPCTeam.py:78-88, py/src/DMPCPlayer.py:27-55), checked on hand-worked states."""
+    from robo_game_sim_b200 import sampler as sp
+
+    s = np.zeros(22)
+    s[2:6] = [1.0, 0.5, 0.0, 0.0]
+    assert sp.dmpc_play(s, field=-1) == sp.OFFENSE
+    s[2] = 8.0                                   # field * px = 8 > 10 - 2.5
+    assert sp.dmpc_play(s, field=1) == sp.DEFENSE
+    s[2], s[4] = 6.0, 2.0                        # 6 > 10 - 5 and vx 2 > 1
+    assert sp.dmpc_play(s, field=1) == sp.DEFENSE
+    s[4] = 0.5
+    assert sp.dmpc_play(s, field=1) == sp.OFFENSE
+    s[2:4] = [1.0, 0.0]
+    t = sp.dmpc_target(s, sp.OFFENSE, sp.ATTACKER, field=-1, goal_pos=[5.0, 0.0], home_pos=[-5.0, 0.0])
+    assert np.allclose(t, [1.0, 0.0, 4.0, 0.0])                       # hit towards the goal at v_hit
+    t = sp.dmpc_target(s, sp.DEFENSE, sp.ATTACKER, field=-1, goal_pos=[5.0, 0.0], home_pos=[-5.0, 0.0])
+    assert np.allclose(t, [1.0, 0.0, 8.0, 0.0])                       # 2 * v_hit
+    t = sp.dmpc_target(s, sp.DEFENSE, sp.DEFENDER, field=-1, goal_pos=[5.0, 0.0], home_pos=[-5.0, 0.0])
+    assert np.allclose(t, [-2.0, 0.0, 0.0, 0.0])                      # half way between home and puck
+    t = sp.dmpc_target(s, sp.OFFENSE, sp.DEFENDER, field=-1, goal_pos=[5.0, 0.0], home_pos=[-5.0, 0.0])
+    assert np.allclose(t, [1.0, 0.0, 4.0, 0.0])                       # field * px < 0: hit
+    a = sp.candidate_actions(16, 5, players=(0, 1), seed=3)
+    assert a.shape == (16, 5, 4, 2) and a.dtype == np.float32
+    assert np.all(a[0] == 0) and np.all(a[:, :, 2:] == 0) and np.abs(a[1:, :, :2]).max() <= 10.0 and a[1:, :, :2].std() > 3
+    assert np.array_equal(a, sp.candidate_actions(16, 5, players=(0, 1), seed=3))

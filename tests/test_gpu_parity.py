@@ -323,3 +323,35 @@ def test_monte_carlo_batched_harness(rgs, tmp_path):
     mc.num_runs, mc.T = 64, 1.0
     out3 = rgs.monte_carlo_batched(mc, policy=lambda s: torch.zeros((s.shape[0], 4, 2), device=s.device), mode="fast")
     assert out3["games"] == 64 and out3["live_steps"] == 64 * 21
+
+
+# ------------------------------------------------------------------ K3: shared-state rollout sampling
+def test_rollout_sampler_matches_oracle(rgs):
+    """BASELINE configs[4]: 4096 candidate command sequences x 50 steps from ONE state.  fp64 parity mode:
+    every candidate's final state equals the oracle's bit for bit, so costs agree to rounding and the
+    arg-min is the oracle's; fp32 mode: the device arg-min is the arg-min of the device costs and beats
+    the do-nothing candidate."""
+    from robo_game_sim_b200 import sampler as sp
+
+    C, steps, hold = 4096, 50, 10
+    pd = tl.default_params(winning_score=3)
+    x0, warm = tl.synth_inputs(9, 0, 1, 2, 4)
+    s0 = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), warm, 40, 10)["state"][0]     # a mid-game state
+    acts = sp.candidate_actions(C, steps // hold, players=(0, 1), seed=1, dtype=np.float64)
+    play = sp.dmpc_play(s0, field=-1)
+    x_des = {0: sp.dmpc_target(s0, play, sp.ATTACKER, -1, [5.0, 0.0], [-5.0, 0.0]),
+             1: sp.dmpc_target(s0, play, sp.DEFENDER, -1, [5.0, 0.0], [-5.0, 0.0])}
+    o = tl.oracle_rollout(pd, np.repeat(s0[None], C, 0), acts, steps, hold)["state"]
+    w = np.array(sp.OMEGA_N_MAX)
+    ocost = sum(((o[:, 6 + 4 * p:10 + 4 * p] - x_des[p]) ** 2 * w).sum(1) for p in (0, 1))
+
+    sim = rgs.BatchedGameSim(C, mode="exact", winning_score=3)
+    best, first, cost = sp.sample_rollouts(sim, s0, acts, x_des, n_steps=steps, hold=hold)
+    assert np.array_equal(sim.state().cpu().numpy(), o)
+    assert np.allclose(cost.cpu().numpy(), ocost, rtol=1e-12, atol=0)
+    assert best == int(np.argmin(ocost)) and np.array_equal(first, acts[best, 0, :2])
+
+    fast = rgs.BatchedGameSim(C, mode="fast", winning_score=3)
+    fb, _, fcost = sp.sample_rollouts(fast, s0, acts.astype(np.float32), x_des, n_steps=steps, hold=hold)
+    assert fb == int(torch.argmin(fcost)) and float(fcost[fb]) <= float(fcost[0])
+    assert np.abs(fcost.cpu().numpy() - ocost).max() / ocost.max() < 0.05 or fb == best
