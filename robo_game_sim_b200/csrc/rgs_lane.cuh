@@ -73,6 +73,15 @@ struct LaneScratch {
     RGS_DEV int &I(int w) const { return i[w * stride]; }
 };
 
+// index of the lowest set bit of a non-zero mask
+RGS_DEV int low_bit(unsigned m) {
+#ifdef RGS_HOST_EMU
+    return __builtin_ctz(m);
+#else
+    return __ffs((int)m) - 1;
+#endif
+}
+
 template <typename T>
 struct alignas(2 * sizeof(T)) LaneGK { T g, k; };
 template <typename T>
@@ -239,6 +248,22 @@ struct LaneGame {
         return fm(gx, gx, gy * gy) <= sg * sg;
     }
 
+    // re-scan of body e against every other body except `skip` (its partner is flagged by its own call when
+    // e < partner): flag_pair with e's interval held in registers
+    RGS_DEV void reflag_pairs(int e, int skip, Bits<NPAIR> &pb) const {
+        const T lx = s.F(S::BB + 4 * e), hx = s.F(S::BB + 4 * e + 1), ly = s.F(S::BB + 4 * e + 2), hy = s.F(S::BB + 4 * e + 3);
+        const T sl = Slack<T>::v;
+        const int te = (e == PK);
+#pragma unroll 1
+        for (int o = 0; o < E; ++o) {
+            if (o == e || o == skip) continue;
+            const T gx = tmax(T(0), tmax(lx - s.F(S::BB + 4 * o + 1), s.F(S::BB + 4 * o) - hx));
+            const T gy = tmax(T(0), tmax(ly - s.F(S::BB + 4 * o + 3), s.F(S::BB + 4 * o + 2) - hy));
+            const T sg = P.d.sig[te][o == PK] + sl;
+            if (fm(gx, gx, gy * gy) <= sg * sg) pb.set(o < e ? pair_index(o, e) : pair_index(e, o));
+        }
+    }
+
     // ---- narrow phase: one item searched over the columns (insertCollisions :362-507, one test) ----
     // mirrored single-axis view of body a for wall wk: q = sgn * coordinate, overlap <=> q >= lim
     struct Axis {
@@ -297,13 +322,18 @@ struct LaneGame {
                 if (c0 > kGrid) return kGrid + 1;
             }
         }
-        T px, py, vx, vy;
-        eval(a, c0 - 1, px, py, vx, vy);
-        const T sgn = (wk == WALL_UP || wk == WALL_RIGHT) ? T(1) : T(-1);
-        T pm = sgn * (wk >= 2 ? px : py), vm = sgn * (wk >= 2 ? vx : vy);
-        eval(a, c0, px, py, vx, vy);
-        T p = sgn * (wk >= 2 ? px : py);
-        T w = sgn * (wk >= 2 ? vx : vy) - A.u;
+        // columns c0-1 and c0 on the wall's axis only (the mirrored closed form equals eval() up to the sign)
+        T pm, vm, p, w;
+        if (c0 - 1 < A.cs) {
+            const int ax = wk >= 2 ? 0 : 1;
+            const T sgn = (wk == WALL_UP || wk == WALL_RIGHT) ? T(1) : T(-1);
+            pm = sgn * s.F(S::PRV + 4 * a + ax);
+            vm = sgn * s.F(S::PRV + 4 * a + 2 + ax);
+        } else {
+            axis_at(A, c0 - 1, pm, vm);
+        }
+        axis_at(A, c0, p, w);
+        w = w - A.u;
         const T R = tab->e[A.ty][1].g, k1 = tab->e[A.ty][1].k, uh = A.u * P.d.dt_col;
         const T doff = A.off_t - A.off_b;
         bool was_over = false;
@@ -468,12 +498,11 @@ struct LaneGame {
         int best = -1, binfo = 0;
         T bt = T(0);
 #pragma unroll 1
-        for (int e = 0; e < E; ++e) {
-            if ((qmask >> e) & 1u) {
-                const T te = s.F(S::QT + e);
-                const int info = s.I(S::QI + e);
-                if (best < 0 || te < bt || (te == bt && (info >> 16) > (binfo >> 16))) { best = e; bt = te; binfo = info; }
-            }
+        for (unsigned m = qmask; m != 0u; m &= m - 1u) {  // queued owners only (usually one)
+            const int e = low_bit(m);
+            const T te = s.F(S::QT + e);
+            const int info = s.I(S::QI + e);
+            if (best < 0 || te < bt || (te == bt && (info >> 16) > (binfo >> 16))) { best = e; bt = te; binfo = info; }
         }
         ei = best;
         et = bt;
@@ -485,13 +514,12 @@ struct LaneGame {
     // drop queued events sharing a body with the executed one (:347-352)
     RGS_DEV void prune(unsigned &qmask, int ei, int ej) const {
 #pragma unroll 1
-        for (int e = 0; e < E; ++e) {
-            if ((qmask >> e) & 1u) {
-                int cj = s.I(S::QI + e) & 15;
-                if (cj == 15) cj = -1;
-                const bool drop = (ei == e) || (ei == cj && cj != -1) || (ej == e) || (ej == cj && cj != -1);
-                if (drop) qmask &= ~(1u << e);
-            }
+        for (unsigned m = qmask; m != 0u; m &= m - 1u) {
+            const int e = low_bit(m);
+            int cj = s.I(S::QI + e) & 15;
+            if (cj == 15) cj = -1;
+            const bool drop = (ei == e) || (ei == cj && cj != -1) || (ej == e) || (ej == cj && cj != -1);
+            if (drop) qmask &= ~(1u << e);
         }
     }
 
@@ -704,8 +732,7 @@ struct LaneGame {
                 run_items(wb, pb, owners, base, fmask);
                 if (ri < 0) {
 #pragma unroll 1
-                    for (int e = 0; e < E; ++e)
-                        if ((fmask >> e) & 1u) push(e, qmask, seq);
+                    for (unsigned m = fmask; m != 0u; m &= m - 1u) push(low_bit(m), qmask, seq);  // ascending owners
                 } else {
                     if ((fmask >> ri) & 1u) push(ri, qmask, seq);
                     if (rj >= 0 && ((fmask >> rj) & 1u)) push(rj, qmask, seq);
@@ -735,11 +762,8 @@ struct LaneGame {
                     owners |= 1u << rj;
                     flag_walls(rj, wb);
                 }
-#pragma unroll 1
-                for (int o = 0; o < E; ++o) {
-                    if (o != ei && flag_pair(ei, o)) pb.set(o < ei ? pair_index(o, ei) : pair_index(ei, o));
-                    if (rj >= 0 && o != rj && o != ei && flag_pair(rj, o)) pb.set(o < rj ? pair_index(o, rj) : pair_index(rj, o));
-                }
+                reflag_pairs(ei, -1, pb);
+                if (rj >= 0) reflag_pairs(rj, ei, pb);
                 ++counter;
             }
             if (qmask != 0) ev[RGS_EV_COUNTER_LIMIT]++;

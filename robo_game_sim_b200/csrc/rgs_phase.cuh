@@ -401,8 +401,7 @@ struct PhaseKernel {
         const int ri = s.I(R::RI), rj = s.I(R::RJ);
         if (ri < 0) {
 #pragma unroll 1
-            for (int e = 0; e < E; ++e)
-                if ((fmask >> e) & 1u) G.push(e, qmask, seq);
+            for (unsigned m = fmask; m != 0u; m &= m - 1u) G.push(low_bit(m), qmask, seq);  // ascending owners
         } else {
             if ((fmask >> ri) & 1u) G.push(ri, qmask, seq);
             if (rj >= 0 && ((fmask >> rj) & 1u)) G.push(rj, qmask, seq);
@@ -452,11 +451,8 @@ struct PhaseKernel {
                 owners |= 1u << rj;
                 G.flag_walls(rj, wb);
             }
-#pragma unroll 1
-            for (int o = 0; o < E; ++o) {
-                if (o != ei && G.flag_pair(ei, o)) pb.set(o < ei ? Game::pair_index(o, ei) : Game::pair_index(ei, o));
-                if (rj >= 0 && o != rj && o != ei && G.flag_pair(rj, o)) pb.set(o < rj ? Game::pair_index(o, rj) : Game::pair_index(rj, o));
-            }
+            G.reflag_pairs(ei, -1, pb);
+            if (rj >= 0) G.reflag_pairs(rj, ei, pb);
             ++counter;
             if (wb.any() || pb.any()) {
                 s.I(R::RJ) = rj;
