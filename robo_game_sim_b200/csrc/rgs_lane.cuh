@@ -390,6 +390,56 @@ struct LaneGame {
         py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + (late ? g.oty : g.oby);
     }
 
+    // position and velocity at column c (velocity: same arithmetic as eval())
+    RGS_DEV void posvel_at(const PosSeg &g, int c, T &px, T &py, T &vx, T &vy) const {
+        const int j = c - g.cs;
+        if (j <= 0) {
+            const int w = j < 0 ? S::PRV : S::SP;
+            px = s.F(w + 4 * g.e); py = s.F(w + 4 * g.e + 1); vx = s.F(w + 4 * g.e + 2); vy = s.F(w + 4 * g.e + 3);
+            return;
+        }
+        const LaneGK<T> gk = tab->e[g.ty][j];
+        const T tj = P.d.dt_col * T(j);
+        const bool late = c >= g.fl;
+        px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + (late ? g.otx : g.obx);
+        py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + (late ? g.oty : g.oby);
+        vx = fm(g.wx, gk.g, g.ux);
+        vy = fm(g.wy, gk.g, g.uy);
+    }
+    // how far the relative velocity of two segments can drift from its value at any column: each body's velocity
+    // moves monotonically from its segment-start value to its column-50 value
+    RGS_DEV T drift_bound(int a, int b) const {
+        const int tya = (a == PK), tyb = (b == PK);
+        const T ga = tab->e[tya][kGrid - s.I(S::CS + a)].g, gb = tab->e[tyb][kGrid - s.I(S::CS + b)].g;
+        T e2 = T(0);
+#pragma unroll
+        for (int ax = 0; ax < 2; ++ax) {
+            const T wa = s.F(S::SP + 4 * a + 2 + ax) - s.F(S::CMD + 2 * a + ax), wb = s.F(S::SP + 4 * b + 2 + ax) - s.F(S::CMD + 2 * b + ax);
+            // v_end - v_start = (v0 - u) (R^n - 1)
+            const T ra = wa * (ga - T(1)), rb = wb * (gb - T(1));
+            const T r = (ra < T(0) ? -ra : ra) + (rb < T(0) ? -rb : rb);
+            e2 = fm(r, r, e2);
+        }
+        return skip_sqrt(e2) * T(1.001) + T(1.0e-6);
+    }
+    // Columns that are certainly contact-free after a column where the bodies are apart (conservative advancement).
+    // Relative position d and velocity dv at that column (b minus a), |dv(t) - dv| <= eps afterwards, so
+    // |d(t)| >= |d + dv t| - eps t; the earliest t with |d + dv t| = sig + eps t is the smaller positive root of
+    // A t^2 + 2 B t + C.  64 = never again inside this step.
+    RGS_DEV int free_columns(T dx, T dy, T dvx, T dvy, T ssq, T sig, T eps, T inv_h) const {
+        const T sg = sig + Slack<T>::v;
+        const T C = ssq - sg * sg;
+        if (!(C > T(0))) return 0;
+        const T A = fm(dvx, dvx, dvy * dvy) - eps * eps;
+        const T B = fm(dx, dvx, dy * dvy) - sg * eps;
+        const T disc = fm(B, B, -(A * C));
+        if (disc < T(0)) return 64;
+        const T den = skip_sqrt(disc) - B;
+        if (!(den > T(0))) return 64;
+        const T cols = T(0.98) * C * inv_h / den;
+        return (int)tmin(cols, T(64));
+    }
+
     // same for the pair (a, b); the time is symmetric in (a, b) as in the reference (:482-494).
     // Conservative advancement: while the bodies are apart, the relative speed bound S of the two
     // segments says how many columns can be skipped before they could touch.
@@ -397,32 +447,16 @@ struct LaneGame {
         const int tya = (a == PK), tyb = (b == PK);
         const T thr = P.d.ov_le[tya][tyb], sigma = P.d.sig[tya][tyb];
         const T h = P.d.dt_col;
-        T inv_sh;  // 0.98 / (S h); 0 when a correctOverlap jump is pending (no skipping)
-        {
-            T sx, sy;
-            {
-                const T va0 = s.F(S::SP + 4 * a + 2), ua = s.F(S::CMD + 2 * a), vb0 = s.F(S::SP + 4 * b + 2), ub = s.F(S::CMD + 2 * b);
-                const T va1 = fm(va0 - ua, tab->e[tya][kGrid - s.I(S::CS + a)].g, ua), vb1 = fm(vb0 - ub, tab->e[tyb][kGrid - s.I(S::CS + b)].g, ub);
-                const T alo = tmin(va0, va1), ahi = tmax(va0, va1), blo = tmin(vb0, vb1), bhi = tmax(vb0, vb1);
-                sx = tmax(ahi - blo, bhi - alo);
-            }
-            {
-                const T va0 = s.F(S::SP + 4 * a + 3), ua = s.F(S::CMD + 2 * a + 1), vb0 = s.F(S::SP + 4 * b + 3), ub = s.F(S::CMD + 2 * b + 1);
-                const T va1 = fm(va0 - ua, tab->e[tya][kGrid - s.I(S::CS + a)].g, ua), vb1 = fm(vb0 - ub, tab->e[tyb][kGrid - s.I(S::CS + b)].g, ub);
-                const T alo = tmin(va0, va1), ahi = tmax(va0, va1), blo = tmin(vb0, vb1), bhi = tmax(vb0, vb1);
-                sy = tmax(ahi - blo, bhi - alo);
-            }
-            const T S2 = fm(sx, sx, sy * sy);
-            const bool jump = s.I(S::FL + a) > base || s.I(S::FL + b) > base;
-            inv_sh = jump ? T(0) : T(0.98) / (skip_sqrt(S2) * h + T(1.0e-12));
-        }
+        // no skipping while a correctOverlap jump of either body is still ahead
+        const bool jump = s.I(S::FL + a) > base || s.I(S::FL + b) > base;
+        const T eps = drift_bound(a, b), inv_h = T(1) / h;
         int c = base;
         const PosSeg ga = pos_seg(a), gb = pos_seg(b);
 #pragma unroll 1
         while (c <= kGrid) {
             T ax, ay, avx, avy, bx, by, bvx, bvy;
-            pos_at(ga, c, ax, ay);
-            pos_at(gb, c, bx, by);
+            posvel_at(ga, c, ax, ay, avx, avy);
+            posvel_at(gb, c, bx, by, bvx, bvy);
             const T ex = ax - bx, ey = ay - by;
             const T ssq = fm(ex, ex, ey * ey);
             if (ssq <= thr) {
@@ -437,8 +471,7 @@ struct LaneGame {
                 }
                 ++c;
             } else {
-                const T skip = (skip_sqrt(ssq) - sigma) * inv_sh;
-                c += 1 + (int)tmin(skip, T(64));
+                c += 1 + (jump ? 0 : free_columns(-ex, -ey, bvx - avx, bvy - avy, ssq, sigma, eps, inv_h));
             }
         }
         return kGrid + 1;
@@ -529,29 +562,14 @@ struct LaneGame {
     RGS_DEV void march_pair(int bi, int bj, int base, long long *ev) const {
         const int tyi = (bi == PK), tyj = (bj == PK);
         const T thr = P.d.ov_lt[tyi][tyj], sigma = P.d.sig[tyi][tyj];
-        T inv_sh;
-        {
-            const int rem = kGrid - base;
-            T sx, sy;
-            {
-                const T va0 = s.F(S::SP + 4 * bi + 2), ua = s.F(S::CMD + 2 * bi), vb0 = s.F(S::SP + 4 * bj + 2), ub = s.F(S::CMD + 2 * bj);
-                const T va1 = fm(va0 - ua, tab->e[tyi][rem].g, ua), vb1 = fm(vb0 - ub, tab->e[tyj][rem].g, ub);
-                sx = tmax(tmax(va0, va1) - tmin(vb0, vb1), tmax(vb0, vb1) - tmin(va0, va1));
-            }
-            {
-                const T va0 = s.F(S::SP + 4 * bi + 3), ua = s.F(S::CMD + 2 * bi + 1), vb0 = s.F(S::SP + 4 * bj + 3), ub = s.F(S::CMD + 2 * bj + 1);
-                const T va1 = fm(va0 - ua, tab->e[tyi][rem].g, ua), vb1 = fm(vb0 - ub, tab->e[tyj][rem].g, ub);
-                sy = tmax(tmax(va0, va1) - tmin(vb0, vb1), tmax(vb0, vb1) - tmin(va0, va1));
-            }
-            inv_sh = T(0.98) / (skip_sqrt(fm(sx, sx, sy * sy)) * P.d.dt_col + T(1.0e-12));
-        }
+        const T eps = drift_bound(bi, bj), inv_h = T(1) / P.d.dt_col;
         int c = base + 1;
         PosSeg gi = pos_seg(bi), gj = pos_seg(bj);
 #pragma unroll 1
         while (c <= kGrid) {
-            T ax, ay, bx, by;
-            pos_at(gi, c, ax, ay);
-            pos_at(gj, c, bx, by);
+            T ax, ay, bx, by, avx, avy, bvx, bvy;
+            posvel_at(gi, c, ax, ay, avx, avy);
+            posvel_at(gj, c, bx, by, bvx, bvy);
             const T dx = bx - ax, dy = by - ay;
             const T ssq = fm(dx, dx, dy * dy);
             if (ssq <= thr) {
@@ -571,8 +589,7 @@ struct LaneGame {
                 ev[RGS_EV_OVERLAP_FIXES]++;
                 ++c;
             } else {
-                const T skip = (skip_sqrt(ssq) - sigma) * inv_sh;
-                c += 1 + (int)tmin(skip, T(64));
+                c += 1 + free_columns(dx, dy, bvx - avx, bvy - avy, ssq, sigma, eps, inv_h);
             }
         }
     }
