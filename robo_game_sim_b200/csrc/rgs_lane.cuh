@@ -1011,7 +1011,19 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
     }
     double sa = srec[0], sb = srec[1];
     double t_clock = A.clock[game];
+    // The event record is updated from divergent code with run-time indices.  In global memory every lane's record
+    // is its own 128-byte line (32 lines per warp access); a thread-local copy is interleaved across the lanes.
+#ifndef RGS_EV_IN_GLOBAL
+    long long evloc[RGS_N_EVENTS];
+    {
+        const long long *g0 = A.events + game * RGS_N_EVENTS;
+#pragma unroll
+        for (int i = 0; i < RGS_N_EVENTS; ++i) evloc[i] = g0[i];
+    }
+    long long *gev = evloc;
+#else
     long long *gev = A.events + game * RGS_N_EVENTS;
+#endif
     double *dmg = A.damage + game * (NP * NP);
     long long live = gev[RGS_EV_LIVE_STEPS], loop_iters = gev[RGS_EV_LOOP_ITERS], decided = gev[RGS_EV_DECIDED_STEP];
     const T *actions = static_cast<const T *>(A.actions);
@@ -1079,6 +1091,13 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
     gev[RGS_EV_LIVE_STEPS] = live;
     gev[RGS_EV_LOOP_ITERS] = loop_iters;
     gev[RGS_EV_DECIDED_STEP] = decided;
+#ifndef RGS_EV_IN_GLOBAL
+    {
+        long long *g0 = A.events + game * RGS_N_EVENTS;
+#pragma unroll
+        for (int i = 0; i < RGS_N_EVENTS; ++i) g0[i] = evloc[i];
+    }
+#endif
 }
 
 }  // namespace rgs

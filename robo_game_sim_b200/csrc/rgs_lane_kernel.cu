@@ -33,11 +33,14 @@ __global__ void __launch_bounds__(THREADS) rollout_lane_kernel(const __grid_cons
 }
 
 template <typename T, int NT>
-static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count) {
-    using S = LaneScratch<T, NT>;
-    constexpr int kThreads = 64;
-    constexpr size_t tab_bytes = (sizeof(LaneTab<T>) + 15) & ~size_t(15);
-    size_t smem = tab_bytes + ((size_t)S::NF * sizeof(T) + (size_t)S::NI * sizeof(int)) * kThreads;
+constexpr size_t lane_smem_bytes(int threads) {
+    return ((sizeof(LaneTab<T>) + 15) & ~size_t(15)) +
+           ((size_t)LaneScratch<T, NT>::NF * sizeof(T) + (size_t)LaneScratch<T, NT>::NI * sizeof(int)) * threads;
+}
+
+template <typename T, int NT, int kThreads>
+static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count) {
+    size_t smem = lane_smem_bytes<T, NT>(kThreads);
 #ifdef RGS_EXP_ONLY_2V2
     if (const char *pad = std::getenv("RGS_EXP_SMEM_PAD")) smem += (size_t)std::atoi(pad);  // occupancy sensitivity experiments
 #endif
@@ -50,10 +53,25 @@ static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cuda
     if (per_sm < 1) per_sm = 1;
     int64_t blocks = (A.n_games + kThreads - 1) / kThreads;
     const int64_t cap = (int64_t)sm_count * per_sm;  // persistent grid: resident CTAs x SM count
-    if (blocks > cap) blocks = cap;
+    if (blocks > cap) blocks = cap;  // (equalising the rounds per lane was measured: no gain, profiles/r01_ab_variants.md)
     if (blocks < 1) blocks = 1;
     kern<<<(unsigned)blocks, kThreads, smem, stream>>>(P, A);
     return cudaGetLastError();
+}
+
+// CTA size: measured on B200 (profiles/r01_ab_variants.md), 128 lanes per CTA (3 CTAs = 12 warps per SM for
+// 2v2 fp32) run 10 % faster than 64 (7 CTAs); 256 and 512 are level with 128, 192 / 320 / 384 clearly worse.
+// Records too large for two 128-lane CTAs per SM keep 64; batches smaller than one 128-lane CTA per SM (the
+// K3 sampler's 4096 candidates) use one warp per CTA so that they spread over all SMs.
+template <typename T, int NT>
+static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count) {
+#ifdef RGS_LANE_THREADS
+    return launch_lane_sized<T, NT, RGS_LANE_THREADS>(P, A, stream, sm_count);
+#else
+    constexpr int kBig = lane_smem_bytes<T, NT>(128) <= 110 * 1024 ? 128 : 64;
+    if (A.n_games < (int64_t)sm_count * kBig) return launch_lane_sized<T, NT, 32>(P, A, stream, sm_count);
+    return launch_lane_sized<T, NT, kBig>(P, A, stream, sm_count);
+#endif
 }
 
 template <typename T>
