@@ -313,6 +313,7 @@ int rgs_batch_run(rgs_batch *b, const void *d_actions, int64_t n_act, int64_t ho
                   int64_t n_steps, int64_t log_stride, double *d_traj, void *stream) {
     int rc = check_run_args(b, n_act, hold, n_steps, log_stride, d_traj);
     if (rc != RGS_OK) return rc;
+    if (b->n_games == 0) return RGS_OK;  // an empty batch has no command tensor to point at
     if (!d_actions) return fail(RGS_EINVAL, "d_actions is NULL");
     if (act_game_stride < 0) return fail(RGS_EINVAL, "act_game_stride must be >= 0");
     DeviceGuard guard(b->device);

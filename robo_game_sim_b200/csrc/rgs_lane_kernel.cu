@@ -13,7 +13,10 @@
 namespace rgs {
 
 template <typename T, int NT, int THREADS>
-__global__ void __launch_bounds__(THREADS) rollout_lane_kernel(const __grid_constant__ FastParams<T> P,
+#ifndef RGS_LANE_MINBLOCKS
+#define RGS_LANE_MINBLOCKS 1
+#endif
+__global__ void __launch_bounds__(THREADS, RGS_LANE_MINBLOCKS) rollout_lane_kernel(const __grid_constant__ FastParams<T> P,
                                                                const __grid_constant__ RunArgs A) {
     using S = LaneScratch<T, NT>;
     extern __shared__ __align__(16) unsigned char smem_raw[];

@@ -51,7 +51,9 @@ def _assert_bit_exact(o, g):
 
 # ------------------------------------------------------------------ K1: fp64 parity mode
 def test_exact_bit_exact_s0_2v2(rgs):
-    n, steps, hold = 4096, 200, 10
+    """North star: "fp64 mode matching the reference's goal/score events bit-exactly over 10^4 randomized games"
+    -- here every state double, clock, damage entry and event record of 10^4 S0 games x 200 steps."""
+    n, steps, hold = 10_000, 200, 10
     pd = tl.default_params(winning_score=3)
     x0, acts = tl.synth_inputs(42, 0, n, 2, steps // hold)
     o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), acts, steps, hold)
@@ -355,3 +357,29 @@ def test_rollout_sampler_matches_oracle(rgs):
     fb, _, fcost = sp.sample_rollouts(fast, s0, acts.astype(np.float32), x_des, n_steps=steps, hold=hold)
     assert fb == int(torch.argmin(fcost)) and float(fcost[fb]) <= float(fcost[0])
     assert np.abs(fcost.cpu().numpy() - ocost).max() / ocost.max() < 0.05 or fb == best
+
+
+@pytest.mark.parametrize("n", [0, 1, 33, 18943, 18945])
+def test_ragged_batch_sizes_and_cta_size_switch(rgs, n):
+    """Empty, single-game and ragged batches, and both sides of the batch size at which the lane kernel switches
+    from one-warp CTAs to 128-lane CTAs (148 SMs x 128): the first and last games equal the emulator build of the
+    same source bit for bit (fp32), and the whole batch equals the oracle in fp64 parity mode (small n)."""
+    steps, hold = 60, 10
+    pd = tl.default_params(winning_score=2)
+    if n == 0:
+        sim = rgs.BatchedGameSim(0, mode="fast")
+        sim.reset()
+        sim.run(torch.zeros((0, 1, 4, 2), dtype=torch.float32, device="cuda"), n_steps=steps)
+        assert sim.state().shape == (0, 22) and int(sim.stats()[0]) == 0
+        return
+    x0, acts = tl.synth_inputs(31, 0, n, 2, steps // hold)
+    _, g = _gpu_rollout(rgs, "fast", pd, x0, acts.astype(np.float32), steps, hold)
+    pick = np.unique(np.r_[np.arange(min(n, 40)), np.arange(max(0, n - 40), n)])
+    e = tl.emu_rollout(dict(pd, mode=tl.MODE_FAST_F32), tl.oracle_reset(pd, x0[pick]), acts[pick], steps, hold)
+    assert np.array_equal(e["state"], g["state"][pick]) and np.array_equal(e["events"], g["events"][pick])
+    assert np.array_equal(e["damage"], g["damage"][pick]) and np.array_equal(e["t"], g["t"][pick])
+    assert int(g["stats"][0]) == n and g["events"][:, tl.EV["LIVE_STEPS"]].max() == steps
+    if n <= 33:
+        o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), acts, steps, hold)
+        _, x = _gpu_rollout(rgs, "exact", pd, x0, acts, steps, hold)
+        _assert_bit_exact(o, x)
