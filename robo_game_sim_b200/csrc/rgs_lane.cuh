@@ -628,7 +628,8 @@ struct LaneGame {
     // ---- execute one popped event (carryOutFirstCollision :237-345): advance the bodies to the time of
     // impact, resolve, start their new segments at column `base`, correctOverlap on the later columns.
     // Returns the second body to re-scan (-1 for a wall event); goal = 1 (team A) / 2 (team B) / 0.
-    RGS_DEV_BIG int resolve(int ei, int ej, int ekind, T et, int &base, int &goal, long long *ev, double *dmg, long long live) const {
+    RGS_DEV_BIG int resolve(int ei, int ej, int ekind, T et, int &base, int &goal, long long *ev, double *dmg, long long live,
+                            double *dv_sq_out = nullptr) const {
         int rj = -1;
         goal = 0;
         {
@@ -669,6 +670,7 @@ struct LaneGame {
                 const T fi = P.d.imp_coef[tyi][tyj] * dot / nn, fj = P.d.imp_coef[tyj][tyi] * dot / nn;
                 if (ei != PK && ej != PK) {  // damage :277-282
                     const double dv_sq = 0.01 * ((double)dvx * (double)dvx + (double)dvy * (double)dvy);
+                    if (dv_sq_out) *dv_sq_out = dv_sq;
                     dmg[ei * NP + ej] += (double)P.d.mass[tyi] * dv_sq;
                     dmg[ej * NP + ei] += (double)P.d.mass[tyj] * dv_sq;
                     ev[RGS_EV_PLAYER_PLAYER]++;
@@ -735,6 +737,124 @@ struct LaneGame {
         return rj;
     }
 
+    // ---- jammed steps ------------------------------------------------------------------------------------
+    // 0.03 % of the S0 steps run the event loop to its bound of 50 (:150): two bodies (and a wall) resolved at
+    // the same instant over and over.  Every resolution restarts from the unchanged column base-1, so the loop
+    // state becomes PERIODIC (period 2 or 3) after a few iterations.  Once the whole loop state at the top of an
+    // iteration equals, bit for bit, the state a few iterations earlier, the remaining whole periods are not
+    // executed: their side effects (event counters, the order-sensitive event hash, damage, push sequence
+    // numbers) are replayed exactly and the loop resumes for the last partial period.  Identical results,
+    // ~10 % fewer instructions overall (those steps were 12 % of them).
+    static constexpr bool kJamFF = NT <= 3;
+    static constexpr int kJamLog = 6;
+    struct JamSnap {
+        T f[S::QT + E];                 // SP, CMD, PRV, OFF, BB, and QT of the queued owners
+        int i[3 * E];                   // CS, FL, QI & 0xFFFF of the queued owners
+        unsigned qmask, owners, wbits, pbits, ranks;
+        int base, ri, rj, scored, seq, counter;
+        long long ev[RGS_N_EVENTS];
+        int log_n, log_ev[kJamLog];     // kind | i << 4 | (j + 1) << 8 | goal << 12 per executed / discarded event
+        double log_dv[kJamLog];         // dv_sq of a player-player impact, else -1
+    };
+    static RGS_DEV bool same_bits(T a, T b) {
+        if constexpr (sizeof(T) == 4) {
+            unsigned x, y;
+            memcpy(&x, &a, 4); memcpy(&y, &b, 4);
+            return x == y;
+        } else {
+            unsigned long long x, y;
+            memcpy(&x, &a, 8); memcpy(&y, &b, 8);
+            return x == y;
+        }
+    }
+    // order of the queued owners by push sequence number (the tie rule of pop() only sees this order)
+    RGS_DEV unsigned queue_ranks(unsigned qmask) const {
+        unsigned r = 0;
+#pragma unroll 1
+        for (unsigned m = qmask; m != 0u; m &= m - 1u) {
+            const int e = low_bit(m);
+            const int se = s.I(S::QI + e) >> 16;
+            int rank = 0;
+#pragma unroll 1
+            for (unsigned m2 = qmask; m2 != 0u; m2 &= m2 - 1u) rank += (s.I(S::QI + low_bit(m2)) >> 16) < se;
+            r |= (unsigned)rank << (3 * e);
+        }
+        return r;
+    }
+    RGS_DEV void jam_snapshot(JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
+                              bool scored, int seq, int counter, const long long *ev) const {
+#pragma unroll 1
+        for (int w = 0; w < S::QT; ++w) J.f[w] = s.F(w);
+#pragma unroll 1
+        for (int e = 0; e < E; ++e) {
+            J.f[S::QT + e] = s.F(S::QT + e);
+            J.i[e] = s.I(S::CS + e);
+            J.i[E + e] = s.I(S::FL + e);
+            J.i[2 * E + e] = s.I(S::QI + e) & 0xFFFF;
+        }
+        J.qmask = qmask; J.owners = owners; J.wbits = wbits; J.pbits = pbits; J.ranks = queue_ranks(qmask);
+        J.base = base; J.ri = ri; J.rj = rj; J.scored = scored; J.seq = seq; J.counter = counter;
+#pragma unroll 1
+        for (int k = 0; k < RGS_N_EVENTS; ++k) J.ev[k] = ev[k];
+        J.log_n = 0;
+    }
+    RGS_DEV bool jam_same(const JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
+                          bool scored) const {
+        if (J.qmask != qmask || J.owners != owners || J.wbits != wbits || J.pbits != pbits || J.base != base || J.ri != ri ||
+            J.rj != rj || J.scored != (int)scored)
+            return false;
+#pragma unroll 1
+        for (int w = 0; w < S::QT; ++w)
+            if (!same_bits(J.f[w], s.F(w))) return false;
+#pragma unroll 1
+        for (int e = 0; e < E; ++e) {
+            if (J.i[e] != s.I(S::CS + e) || J.i[E + e] != s.I(S::FL + e)) return false;
+            if ((qmask >> e) & 1u)
+                if (!same_bits(J.f[S::QT + e], s.F(S::QT + e)) || J.i[2 * E + e] != (s.I(S::QI + e) & 0xFFFF)) return false;
+        }
+        return J.ranks == queue_ranks(qmask);
+    }
+    // skip the whole periods that fit before the loop bound; returns the new counter
+    RGS_DEV int jam_fast_forward(const JamSnap &J, int counter, int &seq, unsigned qmask, long long *ev, double *dmg, long long live) const {
+        const int period = counter - J.counter;
+        const int m = (kCounterLim - counter) / period;
+        if (m <= 0 || J.log_n != period) return counter;
+        RGS_TRACE("jam fast-forward: live %lld counter %d period %d skipped %d\n", live, counter, period, m * period);
+        static constexpr int kAdd[] = {RGS_EV_GOALS_A, RGS_EV_GOALS_B, RGS_EV_WALL_UP, RGS_EV_WALL_DOWN, RGS_EV_WALL_RIGHT,
+                                       RGS_EV_WALL_LEFT, RGS_EV_PLAYER_PLAYER, RGS_EV_PLAYER_PUCK, RGS_EV_DISCARDED,
+                                       RGS_EV_BASE_CLAMP, RGS_EV_OVERLAP_FIXES};
+#pragma unroll 1
+        for (int k = 0; k < (int)(sizeof(kAdd) / sizeof(int)); ++k) ev[kAdd[k]] += (long long)m * (ev[kAdd[k]] - J.ev[kAdd[k]]);
+#pragma unroll 1
+        for (int r = 0; r < m; ++r)
+#pragma unroll 1
+            for (int l = 0; l < period; ++l) {
+                const int c = J.log_ev[l];
+                const int kind = c & 15, i = (c >> 4) & 15, j = ((c >> 8) & 15) - 1, goal = (c >> 12) & 3;
+                hash_event(ev, live, kind, i, j, goal);
+                if (J.log_dv[l] >= 0.0) {  // damage :277-282, same operands in the same order
+                    dmg[i * NP + j] += (double)P.d.mass[i == PK] * J.log_dv[l];
+                    dmg[j * NP + i] += (double)P.d.mass[j == PK] * J.log_dv[l];
+                }
+            }
+        // the sequence numbers of the queued events advance by whole periods too (their order is what matters)
+        const int dseq = m * (seq - J.seq);
+#pragma unroll 1
+        for (unsigned q = qmask; q != 0u; q &= q - 1u) {
+            const int e = low_bit(q);
+            if ((s.I(S::QI + e) >> 16) >= J.seq) s.I(S::QI + e) += dseq << 16;
+        }
+        seq += dseq;
+        return counter + m * period;
+    }
+    RGS_DEV void jam_log(JamSnap &J, int kind, int i, int j, int goal, double dv_sq) const {
+        if (J.log_n < kJamLog) {
+            J.log_ev[J.log_n] = kind | (i << 4) | ((j + 1) << 8) | (goal << 12);
+            J.log_dv[J.log_n] = dv_sq;
+        }
+        J.log_n++;
+    }
+
     // ---- the event loop of one game-step (GameSim::updateSim :136-150) on the flagged items ----
     // returns the loop counter of the step
     RGS_DEV int event_loop(Bits<4 * E> &wb, Bits<NPAIR> &pb, double &sa, double &sb, long long *ev, double *dmg, long long live) const {
@@ -743,8 +863,21 @@ struct LaneGame {
             unsigned qmask = 0, fmask = 0, owners = (1u << E) - 1u;
             int seq = 0, base = 1, ri = -1, rj = -1;
             bool scored = false;
+            JamSnap J;
+            J.counter = 0;  // no snapshot yet
 #pragma unroll 1
             for (;;) {
+                if constexpr (kJamFF) {
+                    if (counter >= 8) {
+                        if ((counter & 7) == 0) {
+                            jam_snapshot(J, qmask, owners, wb.w[0], pb.w[0], base, ri, rj, scored, seq, counter, ev);
+                        } else if (J.counter != 0 && counter - J.counter <= kJamLog &&
+                                   jam_same(J, qmask, owners, wb.w[0], pb.w[0], base, ri, rj, scored)) {
+                            counter = jam_fast_forward(J, counter, seq, qmask, ev, dmg, live);
+                            J.counter = 0;
+                        }
+                    }
+                }
                 fmask = 0;
                 run_items(wb, pb, owners, base, fmask);
                 if (ri < 0) {
@@ -762,11 +895,16 @@ struct LaneGame {
                 if ((ei == PK || ej == PK) && scored) {  // :230-231
                     ev[RGS_EV_DISCARDED]++;
                     hash_event(ev, live, DISCARD, ei, ej, 0);
+                    if constexpr (kJamFF)
+                        if (J.counter != 0) jam_log(J, DISCARD, ei, ej, 0, -1.0);
                     ++counter;
                     continue;
                 }
                 int goal = 0;
-                rj = resolve(ei, ej, ekind, et, base, goal, ev, dmg, live);
+                double dv_sq = -1.0;
+                rj = resolve(ei, ej, ekind, et, base, goal, ev, dmg, live, &dv_sq);
+                if constexpr (kJamFF)
+                    if (J.counter != 0) jam_log(J, ekind, ei, ej, goal, dv_sq);
                 if (goal) {
                     if (goal == 1) sa += 1.0; else sb += 1.0;
                     scored = true;
