@@ -2,7 +2,7 @@
 // ONE LANE PER GAME.
 //
 // Why not a warp per game here (K1 keeps that mapping): the first B200 profile of the warp-per-game
-// throughput kernel (profiles/r01_k2_warp_per_game.md) showed 666 warp-instructions per game-step,
+// throughput kernel (4.7e8 game-steps/s, profiles/r01_bench_first.json) showed 666 warp-instructions per game-step,
 // 45 % of them in a per-column broad phase that finds nothing in 3 steps out of 4, the rest in a
 // serial event path in which 31 lanes idle, and the issue slots 72 % empty on instruction-fetch
 // stalls (78 KB of divergent code).  Games are independent, so the natural SIMT mapping of a huge
@@ -23,10 +23,12 @@
 //     stays inside [p + min(0, vmin T), p + max(0, vmax T)]; bodies whose intervals (inflated by the
 //     radii) cannot meet a wall or each other are never column-tested.  The bound is conservative,
 //     so the events found are the ones the full column scan (insertCollisions :360-511) finds;
-//   * narrow phase: flagged (body, wall) and (body, body) ITEMS are marched over the columns with
-//     the one-column affine map; an item's first column with a valid time of impact is folded into
-//     its owner bodies with the reference's candidate order (walls UP, DOWN, RIGHT, LEFT, then the
-//     other bodies in entity order; strict '<' keeps the first);
+//   * narrow phase: flagged (body, wall) and (body, body) ITEMS are searched over the columns: a wall
+//     item by bisection on the (convex or concave) coordinate along the wall's axis, a pair item by
+//     conservative advancement (columns that the relative motion proves contact-free are skipped);
+//     an item's first column with a valid time of impact is folded into its owner bodies with the
+//     reference's candidate order (walls UP, DOWN, RIGHT, LEFT, then the other bodies in entity
+//     order; strict '<' keeps the first);
 //   * events are resolved exactly like K2's warp formulation did (rgs_fast.cuh history): advance
 //     to the impact time with the RK4 polynomial, 1.01 overlap push, elastic impulse, damage,
 //     advance to the next column, correctOverlap on every later column.
