@@ -222,8 +222,15 @@ def main():
 
     from robo_game_sim_b200 import BatchedGameSim, _capi, synth_inputs
 
-    # stdout carries exactly one JSON line: NCCL's own messages (the version banner at NCCL_DEBUG >= VERSION) go to stderr
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # stdout carries exactly one JSON line: anything native libraries print there (NCCL's version banner) is sent
+    # to stderr by pointing fd 1 at fd 2 for the duration of the run; the line itself goes to the saved descriptor
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
+
+    def emit(line):
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -375,7 +382,7 @@ def main():
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline,
             "stats": {"live_game_steps_per_pass": live_per_pass, "games": int(st[0]), "goals": int(st[8] + st[9]),
                       "events_per_step": float(st[10:16].sum()) / max(1, live_per_pass)}}
-    print(json.dumps(line))
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
 
