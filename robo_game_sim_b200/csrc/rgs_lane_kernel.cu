@@ -17,21 +17,26 @@ template <typename T, int NT, int THREADS>
 #define RGS_LANE_MINBLOCKS 1
 #endif
 __global__ void __launch_bounds__(THREADS, RGS_LANE_MINBLOCKS) rollout_lane_kernel(const __grid_constant__ FastParams<T> P,
-                                                               const __grid_constant__ RunArgs A) {
+                                                               const __grid_constant__ RunArgs A, const int lanes) {
+    // `lanes` = games per CTA.  It equals THREADS except in the one-warp instantiation used for small batches
+    // (launch_lane_nt), where a CTA may carry fewer games than it has threads: a latency-bound batch finishes sooner
+    // on many thin warps (less divergence per warp, more warps per scheduler) than on a few full ones.
     using S = LaneScratch<T, NT>;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     LaneTab<T> *tab = reinterpret_cast<LaneTab<T> *>(smem_raw);
     constexpr size_t tab_bytes = (sizeof(LaneTab<T>) + 15) & ~size_t(15);
+    const int per_cta = THREADS == 32 ? lanes : THREADS;
     T *fw = reinterpret_cast<T *>(smem_raw + tab_bytes);
-    int *iw = reinterpret_cast<int *>(fw + (size_t)S::NF * THREADS);
+    int *iw = reinterpret_cast<int *>(fw + (size_t)S::NF * per_cta);
     for (int i = threadIdx.x; i < 2 * kCols; i += THREADS) {
         (&tab->e[0][0])[i].g = (&P.tab_g[0][0])[i];
         (&tab->e[0][0])[i].k = (&P.tab_k[0][0])[i];
     }
     __syncthreads();
-    const S s{fw + threadIdx.x, iw + threadIdx.x, THREADS};
-    const int64_t stride = (int64_t)gridDim.x * THREADS;
-    for (int64_t game = (int64_t)blockIdx.x * THREADS + threadIdx.x; game < A.n_games; game += stride)
+    if ((int)threadIdx.x >= per_cta) return;
+    const S s{fw + threadIdx.x, iw + threadIdx.x, per_cta};
+    const int64_t stride = (int64_t)gridDim.x * per_cta;
+    for (int64_t game = (int64_t)blockIdx.x * per_cta + threadIdx.x; game < A.n_games; game += stride)
         rollout_lane_game<T, NT>(P, A, tab, s, game);
 }
 
@@ -42,8 +47,9 @@ constexpr size_t lane_smem_bytes(int threads) {
 }
 
 template <typename T, int NT, int kThreads>
-static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count) {
-    size_t smem = lane_smem_bytes<T, NT>(kThreads);
+static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count,
+                                     int lanes = kThreads) {
+    size_t smem = lane_smem_bytes<T, NT>(lanes);
 #ifdef RGS_EXP_ONLY_2V2
     if (const char *pad = std::getenv("RGS_EXP_SMEM_PAD")) smem += (size_t)std::atoi(pad);  // occupancy sensitivity experiments
 #endif
@@ -54,25 +60,34 @@ static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, c
     err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem);
     if (err != cudaSuccess) return err;
     if (per_sm < 1) per_sm = 1;
-    int64_t blocks = (A.n_games + kThreads - 1) / kThreads;
+    int64_t blocks = (A.n_games + lanes - 1) / lanes;
     const int64_t cap = (int64_t)sm_count * per_sm;  // persistent grid: resident CTAs x SM count
     if (blocks > cap) blocks = cap;  // (equalising the rounds per lane was measured: no gain, profiles/r01_ab_variants.md)
     if (blocks < 1) blocks = 1;
-    kern<<<(unsigned)blocks, kThreads, smem, stream>>>(P, A);
+    kern<<<(unsigned)blocks, kThreads, smem, stream>>>(P, A, lanes);
     return cudaGetLastError();
 }
 
 // CTA size: measured on B200 (profiles/r01_ab_variants.md), 128 lanes per CTA (3 CTAs = 12 warps per SM for
 // 2v2 fp32) run 10 % faster than 64 (7 CTAs); 256 and 512 are level with 128, 192 / 320 / 384 clearly worse.
 // Records too large for two 128-lane CTAs per SM keep 64; batches smaller than one 128-lane CTA per SM (the
-// K3 sampler's 4096 candidates) use one warp per CTA so that they spread over all SMs.
+// K3 sampler's 4096 candidates) use one-warp CTAs carrying only a few games each, so that they spread over all SMs.
 template <typename T, int NT>
 static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count) {
 #ifdef RGS_LANE_THREADS
     return launch_lane_sized<T, NT, RGS_LANE_THREADS>(P, A, stream, sm_count);
 #else
     constexpr int kBig = lane_smem_bytes<T, NT>(128) <= 110 * 1024 ? 128 : 64;
-    if (A.n_games < (int64_t)sm_count * kBig) return launch_lane_sized<T, NT, 32>(P, A, stream, sm_count);
+    if (A.n_games < (int64_t)sm_count * kBig) {
+        // games per one-warp CTA: aim at 7 warps per SM.  Measured on the 4096 x 50-step sampler tick
+        // (profiles/r01_configs.json): 32 lanes 2.36 ms, 8 lanes 1.84, 4 lanes (6.9 warps/SM) 1.54, 2 lanes 1.87,
+        // 1 lane (28 warps/SM, instruction-fetch-bound) 2.64.
+        int lanes = (int)((A.n_games + (int64_t)sm_count * 7 - 1) / ((int64_t)sm_count * 7));
+        if (const char *e = std::getenv("RGS_SMALL_LANES")) lanes = std::atoi(e);  // tuning knob
+        if (lanes < 1) lanes = 1;
+        if (lanes > 32) lanes = 32;
+        return launch_lane_sized<T, NT, 32>(P, A, stream, sm_count, lanes);
+    }
     return launch_lane_sized<T, NT, kBig>(P, A, stream, sm_count);
 #endif
 }
