@@ -928,12 +928,97 @@ struct LaneGame {
         return counter;
     }
 
+    // ---- event_loop cut at its iteration boundary (rollout_lane_warp below): the loop-carried variables live in
+    // EvState so that a lane can stop after any iteration and continue later, when enough lanes of its warp are
+    // in the loop too.  event_begin + event_iter until it returns true == event_loop, statement for statement.
+    struct EvState {
+        Bits<4 * E> wb;
+        Bits<NPAIR> pb;
+        unsigned qmask, owners;
+        int seq, base, ri, rj, counter;
+        bool scored;
+    };
+    // (the jam snapshot J is passed separately: its run-time-indexed arrays live in local memory, and a struct that
+    // held both would drag the scalars above there too)
+    RGS_DEV void event_begin(EvState &X, JamSnap &J) const {
+        X.qmask = 0; X.owners = (1u << E) - 1u;
+        X.seq = 0; X.base = 1; X.ri = -1; X.rj = -1; X.counter = 1;
+        X.scored = false;
+        J.counter = 0;
+    }
+    // returns true when the step has no more events to process (X.counter = the loop counter of the step)
+    RGS_DEV bool event_iter(EvState &X, JamSnap &J, double &sa, double &sb, long long *ev, double *dmg, long long live) const {
+        if constexpr (kJamFF) {
+            if (X.counter >= 8) {
+                if ((X.counter & 7) == 0) {
+                    jam_snapshot(J, X.qmask, X.owners, X.wb.w[0], X.pb.w[0], X.base, X.ri, X.rj, X.scored, X.seq, X.counter, ev);
+                } else if (J.counter != 0 && X.counter - J.counter <= kJamLog &&
+                           jam_same(J, X.qmask, X.owners, X.wb.w[0], X.pb.w[0], X.base, X.ri, X.rj, X.scored)) {
+                    X.counter = jam_fast_forward(J, X.counter, X.seq, X.qmask, ev, dmg, live);
+                    J.counter = 0;
+                }
+            }
+        }
+        unsigned fmask = 0;
+        run_items(X.wb, X.pb, X.owners, X.base, fmask);
+        if (X.ri < 0) {
+#pragma unroll 1
+            for (unsigned m = fmask; m != 0u; m &= m - 1u) push(low_bit(m), X.qmask, X.seq);  // ascending owners
+        } else {
+            if ((fmask >> X.ri) & 1u) push(X.ri, X.qmask, X.seq);
+            if (X.rj >= 0 && ((fmask >> X.rj) & 1u)) push(X.rj, X.qmask, X.seq);
+        }
+        if (X.qmask == 0 || X.counter >= kCounterLim) {
+            if (X.qmask != 0) ev[RGS_EV_COUNTER_LIMIT]++;
+            return true;
+        }
+        int ei, ej, ekind;
+        T et;
+        pop(X.qmask, ei, ej, ekind, et);
+        X.ri = ei; X.rj = -1; X.owners = 0;
+        if ((ei == PK || ej == PK) && X.scored) {
+            ev[RGS_EV_DISCARDED]++;
+            hash_event(ev, live, DISCARD, ei, ej, 0);
+            if constexpr (kJamFF)
+                if (J.counter != 0) jam_log(J, DISCARD, ei, ej, 0, -1.0);
+            ++X.counter;
+            return false;
+        }
+        int goal = 0;
+        double dv_sq = -1.0;
+        X.rj = resolve(ei, ej, ekind, et, X.base, goal, ev, dmg, live, &dv_sq);
+        if constexpr (kJamFF)
+            if (J.counter != 0) jam_log(J, ekind, ei, ej, goal, dv_sq);
+        if (goal) {
+            if (goal == 1) sa += 1.0; else sb += 1.0;
+            X.scored = true;
+        }
+        prune(X.qmask, ei, ej);
+        X.owners = 1u << ei;
+        flag_walls(ei, X.wb);
+        if (X.rj >= 0) {
+            X.owners |= 1u << X.rj;
+            flag_walls(X.rj, X.wb);
+        }
+        reflag_pairs(ei, -1, X.pb);
+        if (X.rj >= 0) reflag_pairs(X.rj, ei, X.pb);
+        ++X.counter;
+        return false;
+    }
+
     // ---- one game-step with the state held in shared memory (SP/CMD hold the state and the commands;
     // teams of more than 3, where the register form below would spill) ----
     // returns the event-loop counter of the step (1 when nothing happened)
     RGS_DEV int step(double &sa, double &sb, long long *ev, double *dmg, long long live) const {
         Bits<4 * E> wb;
         Bits<NPAIR> pb;
+        step_head(wb, pb);
+        const int counter = event_loop(wb, pb, sa, sb, ev, dmg, live);
+        step_commit();
+        return counter;
+    }
+    // whole-step segments of all bodies and their broad-phase flags
+    RGS_DEV void step_head(Bits<4 * E> &wb, Bits<NPAIR> &pb) const {
         wb.clear();
         pb.clear();
         {   // whole-step segments: update_bbox + flag_walls with cs = 0 and zero offsets, from registers
@@ -977,15 +1062,15 @@ struct LaneGame {
                 }
             }
         }
-        const int counter = event_loop(wb, pb, sa, sb, ev, dmg, live);
-        // commit column 50 (:153-157)
+    }
+    // commit column 50 (:153-157)
+    RGS_DEV void step_commit() const {
 #pragma unroll 1
         for (int e = 0; e < E; ++e) {
             T px, py, vx, vy;
             eval(e, kGrid, px, py, vx, vy);
             s.F(S::SP + 4 * e) = px; s.F(S::SP + 4 * e + 1) = py; s.F(S::SP + 4 * e + 2) = vx; s.F(S::SP + 4 * e + 3) = vy;
         }
-        return counter;
     }
 
     // ---- the same step with the state in REGISTERS (st[4e+c], cmd[2p+a]; compile-time indices only):
@@ -1238,6 +1323,152 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
         for (int i = 0; i < RGS_N_EVENTS; ++i) g0[i] = evloc[i];
     }
 #endif
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// The same rollout with the WARP as the scheduling unit ("deferred event batching").  rollout_lane_game keeps the
+// 32 games of a warp in lock-step per game-step: every game-step the warp runs the contact-free head (32 lanes)
+// and then the event loop for the few lanes that have contacts (profiles/r01_ncu_lane_v7_full.md: 9.7 of 32
+// lanes active on average, the event path ~4 lanes wide).  Games are independent, so here a lane that meets a
+// contact PARKS in the event loop while the others go on with their next game-steps; the warp executes an event
+// iteration only when `batch` lanes are parked (or nobody is left to advance), and then all of them take it
+// together.  A lane that finishes its game stores it and loads the next one of its stride without waiting for
+// the rest of the warp.  Every game executes exactly the statements rollout_lane_game executes for it, in the
+// same order: results are bit-identical, only the interleaving between lanes differs.
+// ---------------------------------------------------------------------------------------------------------
+RGS_DEV unsigned lane_ballot(bool p) {
+#ifdef RGS_HOST_EMU
+    return p ? 1u : 0u;   // the emulator runs one lane at a time
+#else
+    return __ballot_sync(0xffffffffu, p);
+#endif
+}
+RGS_DEV int lane_popc(unsigned m) {
+#ifdef RGS_HOST_EMU
+    return __builtin_popcount(m);
+#else
+    return __popc(m);
+#endif
+}
+
+template <typename T, int NT>
+RGS_DEV void rollout_lane_warp(const FastParams<T> &P, const RunArgs &A, const LaneTab<T> *tab, const LaneScratch<T, NT> &s,
+                               int64_t game, const int64_t game_stride, const int batch) {
+    constexpr int E = 2 * NT + 1, PK = 2 * NT, SREC = 2 + 4 * E, NP = 2 * NT;
+    using S = LaneScratch<T, NT>;
+    using Game = LaneGame<T, NT>;
+    const Game G(P, tab, s);
+    enum : int { LOAD = 0, HEAD = 1, EVENT = 2, DONE = 3 };
+    int mode = game < A.n_games ? LOAD : DONE;   // lanes without a game still vote
+    // per game
+    double sa = 0.0, sb = 0.0, t_clock = 0.0;
+    long long evloc[RGS_N_EVENTS];
+    long long live = 0, loop_iters = 0, decided = 0;
+    int64_t aidx = 0, phase = 0, k = 0, log_left = 0;
+    bool fetch = true;
+    // per step
+    typename Game::EvState X;
+    typename Game::JamSnap J;
+    const T *actions = static_cast<const T *>(A.actions);
+    const double wsc = (double)P.d.winning_score;
+    const bool logging = A.traj != nullptr && A.log_stride > 0;
+    auto end_step = [&]() {   // the tail of rollout_lane_game's step loop
+        loop_iters += X.counter;
+        t_clock += (double)P.d.dt;
+        ++live;
+        if (decided == 0 && !(sa < wsc && sb < wsc)) decided = live;
+        if (logging && --log_left == 0) {
+            log_left = A.log_stride;
+            write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb);
+        }
+        ++k;
+    };
+#pragma unroll 1
+    for (;;) {
+        const unsigned parked = lane_ballot(mode == EVENT);
+        const unsigned movers = lane_ballot(mode == LOAD || mode == HEAD);
+        if ((parked | movers) == 0u) break;
+        if (lane_popc(parked) >= batch || movers == 0u) {
+            if (mode == EVENT) {
+                if (G.event_iter(X, J, sa, sb, evloc, A.damage + game * (NP * NP), live)) {
+                    G.step_commit();
+                    end_step();
+                    mode = HEAD;
+                }
+            }
+            continue;
+        }
+        if (mode == LOAD) {
+            const double *srec = A.state + game * SREC;
+#pragma unroll 1
+            for (int slot = 0; slot < E; ++slot) {
+                const int e = slot == 0 ? PK : slot - 1;
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const T v = T(srec[2 + 4 * slot + c]);
+                    s.F(S::SP + 4 * e + c) = v;
+                    s.F(S::PRV + 4 * e + c) = v;
+                }
+                s.F(S::CMD + 2 * e) = T(0);
+                s.F(S::CMD + 2 * e + 1) = T(0);
+            }
+            sa = srec[0]; sb = srec[1];
+            t_clock = A.clock[game];
+            const long long *g0 = A.events + game * RGS_N_EVENTS;
+#pragma unroll
+            for (int i = 0; i < RGS_N_EVENTS; ++i) evloc[i] = g0[i];
+            live = evloc[RGS_EV_LIVE_STEPS]; loop_iters = evloc[RGS_EV_LOOP_ITERS]; decided = evloc[RGS_EV_DECIDED_STEP];
+            aidx = A.synth ? A.step0 / A.hold : 0;
+            phase = A.synth ? A.step0 % A.hold : 0;
+            fetch = true;
+            k = 0; log_left = A.log_stride;
+            mode = HEAD;
+        }
+        if (mode == HEAD) {
+            if (k < A.n_steps && sa < wsc && sb < wsc) {  // undecided(), :57-60
+                if (fetch) {
+                    const int64_t ai = (A.synth || aidx < A.n_act) ? aidx : A.n_act - 1;
+#pragma unroll 1
+                    for (int c = 0; c < 2 * NP; ++c)
+                        s.F(S::CMD + c) = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
+                                                  : actions[game * A.act_game_stride + ai * (2 * NP) + c];
+                    fetch = false;
+                }
+                if (++phase == A.hold) { phase = 0; ++aidx; fetch = true; }
+                G.step_head(X.wb, X.pb);
+                if (X.wb.any() || X.pb.any()) {
+                    G.event_begin(X, J);
+                    mode = EVENT;
+                } else {
+                    X.counter = 1;
+                    G.step_commit();
+                    end_step();
+                }
+            } else {
+                if (logging)  // frozen steps of a decided game (GameSim::run :121-123) repeat the frozen state
+                    for (; k < A.n_steps; ++k)
+                        if (--log_left == 0) { log_left = A.log_stride; write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb); }
+                double *srec = A.state + game * SREC;
+                srec[0] = sa;
+                srec[1] = sb;
+#pragma unroll 1
+                for (int slot = 0; slot < E; ++slot) {
+                    const int e = slot == 0 ? PK : slot - 1;
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) srec[2 + 4 * slot + c] = (double)s.F(S::SP + 4 * e + c);
+                }
+                A.clock[game] = t_clock;
+                evloc[RGS_EV_LIVE_STEPS] = live;
+                evloc[RGS_EV_LOOP_ITERS] = loop_iters;
+                evloc[RGS_EV_DECIDED_STEP] = decided;
+                long long *g0 = A.events + game * RGS_N_EVENTS;
+#pragma unroll
+                for (int i = 0; i < RGS_N_EVENTS; ++i) g0[i] = evloc[i];
+                game += game_stride;
+                mode = game < A.n_games ? LOAD : DONE;
+            }
+        }
+    }
 }
 
 }  // namespace rgs

@@ -17,7 +17,7 @@ template <typename T, int NT, int THREADS>
 #define RGS_LANE_MINBLOCKS 1
 #endif
 __global__ void __launch_bounds__(THREADS, RGS_LANE_MINBLOCKS) rollout_lane_kernel(const __grid_constant__ FastParams<T> P,
-                                                               const __grid_constant__ RunArgs A, const int lanes) {
+                                                               const __grid_constant__ RunArgs A, const int lanes, const int batch) {
     // `lanes` = games per CTA.  It equals THREADS except in the one-warp instantiation used for small batches
     // (launch_lane_nt), where a CTA may carry fewer games than it has threads: a latency-bound batch finishes sooner
     // on many thin warps (less divergence per warp, more warps per scheduler) than on a few full ones.
@@ -33,11 +33,17 @@ __global__ void __launch_bounds__(THREADS, RGS_LANE_MINBLOCKS) rollout_lane_kern
         (&tab->e[0][0])[i].k = (&P.tab_k[0][0])[i];
     }
     __syncthreads();
-    if ((int)threadIdx.x >= per_cta) return;
     const S s{fw + threadIdx.x, iw + threadIdx.x, per_cta};
     const int64_t stride = (int64_t)gridDim.x * per_cta;
+#ifdef RGS_LANE_DEB
+    // warp-scheduled form: every thread of the warp votes, threads beyond per_cta own no game
+    const int64_t game = (int)threadIdx.x < per_cta ? (int64_t)blockIdx.x * per_cta + threadIdx.x : A.n_games;
+    rollout_lane_warp<T, NT>(P, A, tab, s, game, stride, batch);
+#else
+    if ((int)threadIdx.x >= per_cta) return;
     for (int64_t game = (int64_t)blockIdx.x * per_cta + threadIdx.x; game < A.n_games; game += stride)
         rollout_lane_game<T, NT>(P, A, tab, s, game);
+#endif
 }
 
 template <typename T, int NT>
@@ -64,7 +70,9 @@ static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, c
     const int64_t cap = (int64_t)sm_count * per_sm;  // persistent grid: resident CTAs x SM count
     if (blocks > cap) blocks = cap;  // (equalising the rounds per lane was measured: no gain, profiles/r01_ab_variants.md)
     if (blocks < 1) blocks = 1;
-    kern<<<(unsigned)blocks, kThreads, smem, stream>>>(P, A, lanes);
+    int batch = 16;  // lanes parked in the event loop before the warp runs an event iteration (RGS_LANE_DEB builds)
+    if (const char *e = std::getenv("RGS_DEB_BATCH")) batch = std::atoi(e);
+    kern<<<(unsigned)blocks, kThreads, smem, stream>>>(P, A, lanes, batch);
     return cudaGetLastError();
 }
 

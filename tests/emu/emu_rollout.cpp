@@ -35,7 +35,7 @@ void run_fast(const rgs_params &p, const rgs::RunArgs &A) {
 }
 
 template <typename T, int NT>
-void run_lane(const rgs_params &p, const rgs::RunArgs &A) {
+void run_lane(const rgs_params &p, const rgs::RunArgs &A, bool warp_sched = false) {
     using S = rgs::LaneScratch<T, NT>;
     auto tab = std::make_unique<rgs::LaneTab<T>>();
     const rgs::FastParams<T> P = rgs::make_fast_params<T>(p);
@@ -44,7 +44,8 @@ void run_lane(const rgs_params &p, const rgs::RunArgs &A) {
     T fw[S::NF];
     int iw[S::NI];
     S s{fw, iw, 1};
-    for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT>(P, A, tab.get(), s, g);
+    if (warp_sched) rgs::rollout_lane_warp<T, NT>(P, A, tab.get(), s, 0, 1, 16);  // one lane walks all the games
+    else for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT>(P, A, tab.get(), s, g);
 }
 
 // The phased block kernel (rgs_phase.cuh), one block of `n_threads` slots; the threads of a phase are
@@ -103,6 +104,8 @@ void dispatch(const rgs_params &p, const rgs::RunArgs &A) {
     else if (p.mode == RGS_MODE_FAST_F64 && warp_k2) run_fast<double, NT>(p, A);
     else if (p.mode == 34) { if constexpr (NT <= 3) run_phase<float, NT>(p, A); }
     else if (p.mode == 67) { if constexpr (NT <= 3) run_phase<double, NT>(p, A); }
+    else if (p.mode == 35) run_lane<float, NT>(p, A, true);    // 35 / 68: the warp-scheduled lane rollout (rollout_lane_warp)
+    else if (p.mode == 68) run_lane<double, NT>(p, A, true);
     else if (p.mode == RGS_MODE_FAST_F32 || p.mode == 33) run_lane<float, NT>(p, A);
     else run_lane<double, NT>(p, A);
 }

@@ -137,3 +137,18 @@ def test_phase_kernel_synth_and_resume():
     h = tl.emu_rollout(pd, s0, acts[:, :3], 30, 10)
     c = tl.emu_rollout(pd, h["state"], acts[:, 3:], 30, 10, t=h["t"], damage=h["damage"], events=h["events"])
     _assert_same(a, c)
+
+
+@pytest.mark.parametrize("n_team,n,steps", [(2, 400, 120), (1, 100, 60), (4, 60, 40)])
+def test_warp_scheduled_rollout_equals_lane_rollout(n_team, n, steps):
+    """rollout_lane_warp (event loop cut at its iteration boundary, games loaded / stored inside the scheduling loop;
+    A/B build -DRGS_LANE_DEB, emulator modes 35 / 68) executes the statements of rollout_lane_game per game: the
+    results must be identical bit for bit, including the strided trajectory log and a resumed rollout."""
+    x0, acts = tl.synth_inputs(5, 0, n, n_team, steps // 10)
+    s0 = tl.oracle_reset(tl.default_params(n_team=n_team), x0)
+    for lane_mode, warp_mode in ((tl.MODE_FAST_F32, 35), (tl.MODE_FAST_F64, 68)):
+        a = tl.emu_rollout(tl.default_params(n_team=n_team, mode=lane_mode), s0, acts, steps, 10, log_stride=20)
+        b = tl.emu_rollout(tl.default_params(n_team=n_team, mode=warp_mode), s0, acts, steps, 10, log_stride=20)
+        _assert_same(a, b)
+        assert np.array_equal(a["traj"], b["traj"])
+        assert a["events"][:, 2:8].sum() > 50
