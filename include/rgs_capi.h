@@ -115,6 +115,28 @@ int rgs_batch_run(rgs_batch *b, const void *d_actions, int64_t n_act, int64_t ho
 int rgs_batch_run_synth(rgs_batch *b, uint64_t seed, int64_t first_game, int64_t step0, int64_t hold, double u_max,
                         int64_t n_steps, int64_t log_stride, double *d_traj, void *stream);
 
+/* Closed-loop rollout on the ON-DEVICE SURROGATE POLICY: every game-step the commands of all
+ * players are computed from the state inside the kernel, so the Monte Carlo loop of py/MonteCarlo.py:35-46
+ * (team_A_run_method, team_B_run_method, optional cbf_run_method, sim.run) never leaves the GPU.
+ * Play selection and target states are the reference's baseline team (py/src/ClassicalTeam.py:32-75,
+ * py/src/ClassicalPlayer.py:190-244); the pydrake minimum-time trajectory optimiser behind them is replaced by
+ * the tracking law u = clamp(v_f + gain (p_f - p), +-input_limit).  cbf != 0 filters the commands through the
+ * reference's control-barrier half-spaces (py/src/CBF.py:36-76, alpha(h) = barrier_gain h^3) with `sweeps`
+ * Hildreth sweeps instead of the pydrake QP.  See robo_game_sim_b200/csrc/rgs_policy.cuh.
+ * FAST modes, players_per_team == 2 (the reference's team size); RGS_EUNSUPPORTED otherwise. */
+typedef struct rgs_policy {
+    double kick_velocity;  /* 4     ClassicalTeam.py:12 */
+    double gain;           /* 4     tracking gain [1/s] of the surrogate law */
+    double input_limit;    /* 10    mc_example_1.py:24 */
+    double safety_radius;  /* 0.4 = 2 * player_radius, mc_example_1.py:35 */
+    double barrier_gain;   /* 30    mc_example_1.py:36 */
+    int32_t cbf;           /* 0 = nominal commands, 1 = barrier filter on (mc_example_1.py:45) */
+    int32_t sweeps;        /* Hildreth sweeps of the filter, e.g. 8 */
+} rgs_policy;
+void rgs_default_policy(rgs_policy *pol);
+int rgs_batch_run_policy(rgs_batch *b, const rgs_policy *pol, int64_t n_steps, int64_t log_stride, double *d_traj,
+                         void *stream);
+
 /* K3, shared-state rollout sampling (BASELINE configs[4]: 4096 candidate command sequences x 50 steps from one
  * state per controller tick).  It takes over the ROLE of the reference's per-tick trajectory optimisation
  * (DMPC.compute_control, reference py/src/DMPC.py:16-54: direct collocation over an internal linear model,

@@ -28,6 +28,12 @@ class RgsParams(C.Structure):
                 ("goal_height", C.c_double), ("mode", C.c_int32), ("reserved", C.c_int32)]
 
 
+class RgsPolicy(C.Structure):
+    """rgs_policy of include/rgs_capi.h (defaults: rgs_default_policy)."""
+    _fields_ = [("kick_velocity", C.c_double), ("gain", C.c_double), ("input_limit", C.c_double),
+                ("safety_radius", C.c_double), ("barrier_gain", C.c_double), ("cbf", C.c_int32), ("sweeps", C.c_int32)]
+
+
 # every symbol include/rgs_capi.h declares: (restype, argtypes)
 _vp, _i64, _i32, _u64, _dbl = C.c_void_p, C.c_int64, C.c_int32, C.c_uint64, C.c_double
 _PP = C.POINTER(RgsParams)
@@ -42,6 +48,8 @@ SIGNATURES = {
     "rgs_batch_reset": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "rgs_batch_run": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp, _vp]),
     "rgs_batch_run_synth": (C.c_int, [_vp, _u64, _i64, _i64, _i64, _dbl, _i64, _i64, _vp, _vp]),
+    "rgs_default_policy": (None, [C.POINTER(RgsPolicy)]),
+    "rgs_batch_run_policy": (C.c_int, [_vp, C.POINTER(RgsPolicy), _i64, _i64, _vp, _vp]),
     "rgs_batch_get": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "rgs_batch_stats": (C.c_int, [_vp, _vp, _vp]),
     "rgs_batch_reset_shared": (C.c_int, [_vp, _vp, _vp]),

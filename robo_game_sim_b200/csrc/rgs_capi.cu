@@ -69,6 +69,7 @@ struct rgs_batch {
     int64_t n_games = 0;
     rgs_params p{};
     int n_team = 2, E = 5, srec = 22, dmg_rec = 16;
+    rgs_policy pol{};      // the on-device policy of the current rgs_batch_run_policy call
     bool warp_k2 = false;  // RGS_K2_WARP=1: the superseded warp-per-game throughput kernel (A/B measurements only)
     bool lane_k2 = true;   // RGS_K2_LANE=0: the phased block kernel (rgs_phase.cuh) instead of one lane per game (A/B; teams <= 3)
     double *state = nullptr, *clock = nullptr, *damage = nullptr;
@@ -119,6 +120,12 @@ int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64
     A.first_game = first_game + g0;
     A.step0 = step0;
     A.u_max = u_max;
+    if (synth == 2) {
+        if (b->p.mode == RGS_MODE_EXACT_F64 || b->n_team != 2 || b->warp_k2 || !b->lane_k2)
+            return fail(RGS_EUNSUPPORTED, "the on-device policy runs in the FAST modes of the lane kernel with players_per_team == 2");
+        A.pol = rgs::PolicyArgs{b->pol.kick_velocity, b->pol.gain, b->pol.input_limit, b->pol.safety_radius,
+                                b->pol.barrier_gain, b->pol.cbf, b->pol.sweeps};
+    }
     cudaError_t e;
     switch (b->p.mode) {
     case RGS_MODE_EXACT_F64:
@@ -328,6 +335,31 @@ int rgs_batch_run_synth(rgs_batch *b, uint64_t seed, int64_t first_game, int64_t
     if (step0 < 0) return fail(RGS_EINVAL, "step0 must be >= 0");
     DeviceGuard guard(b->device);
     return run_range(b, 0, b->n_games, nullptr, 1, hold, 0, n_steps, log_stride, d_traj, 1, seed, first_game, step0, u_max,
+                     static_cast<cudaStream_t>(stream));
+}
+
+void rgs_default_policy(rgs_policy *pol) {
+    if (!pol) return;
+    pol->kick_velocity = 4.0;
+    pol->gain = 4.0;
+    pol->input_limit = 10.0;
+    pol->safety_radius = 0.4;
+    pol->barrier_gain = 30.0;
+    pol->cbf = 0;
+    pol->sweeps = 8;
+}
+
+int rgs_batch_run_policy(rgs_batch *b, const rgs_policy *pol, int64_t n_steps, int64_t log_stride, double *d_traj,
+                         void *stream) {
+    int rc = check_run_args(b, 1, 1, n_steps, log_stride, d_traj);
+    if (rc != RGS_OK) return rc;
+    if (!pol) return fail(RGS_EINVAL, "pol is NULL");
+    if (!(pol->input_limit > 0.0) || !(pol->gain >= 0.0)) return fail(RGS_EINVAL, "policy: input_limit must be > 0 and gain >= 0");
+    if (pol->cbf && (pol->sweeps < 1 || !(pol->barrier_gain > 0.0) || !(pol->safety_radius >= 2.0 * b->p.player_radius)))
+        return fail(RGS_EINVAL, "policy: the barrier filter needs sweeps >= 1, barrier_gain > 0 and safety_radius >= 2 player_radius (CBF.py:29-30)");
+    DeviceGuard guard(b->device);
+    b->pol = *pol;
+    return run_range(b, 0, b->n_games, nullptr, 1, 1, 0, n_steps, log_stride, d_traj, 2, 0, 0, 0, 0.0,
                      static_cast<cudaStream_t>(stream));
 }
 

@@ -55,6 +55,12 @@ struct DevParams {
     int n_team;
 };
 
+// on-device surrogate policy (rgs_policy.cuh); mirrors rgs_policy of include/rgs_capi.h
+struct PolicyArgs {
+    double kick_velocity, gain, input_limit, safety_radius, barrier_gain;
+    int cbf, sweeps;
+};
+
 struct RunArgs {
     int64_t n_games;
     double *state;      // [N, 2+4E]
@@ -65,11 +71,12 @@ struct RunArgs {
     int64_t n_act, hold, act_game_stride;
     int64_t n_steps, log_stride;
     double *traj;
-    // on-chip synthetic actions
+    // command source: 0 the action tensor, 1 on-chip synthetic actions, 2 the on-device policy `pol` (K2 lane kernel)
     int synth;
     uint64_t seed;
     int64_t first_game, step0;
     double u_max;
+    PolicyArgs pol;
 };
 
 // ---- Philox4x32-10 (Salmon et al. 2011), counter-based: keyed by (seed, game, action index) ----

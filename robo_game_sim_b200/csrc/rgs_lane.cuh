@@ -40,6 +40,7 @@
 // source with g++ (no warp emulation needed).  All fused multiply-adds are spelled out (fm()).
 #pragma once
 #include "rgs_fast.cuh"
+#include "rgs_policy.cuh"
 
 // The rollout kernels are instruction-cache-bound before they are issue-bound (profiles/): the large,
 // rarely-converged narrow-phase and resolution functions are compiled once per kernel and CALLED.
@@ -1195,7 +1196,10 @@ RGS_DEV void write_traj_lane(const RunArgs &A, const LaneScratch<T, NT> &s, int6
 
 // all n_steps of ONE game (the body of a lane).  Teams of up to 3: the state lives in registers
 // between steps (step_regs); larger teams keep it in the scratch record (step).
-template <typename T, int NT>
+// kPolicy: the commands come from the on-device surrogate policy (rgs_policy.cuh), evaluated on the state at the
+// start of EVERY game-step (the reference calls the team methods once per step, py/MonteCarlo.py:37-46); a separate
+// instantiation, so that the open-loop kernels do not carry its code.
+template <typename T, int NT, bool kPolicy = false>
 RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const LaneTab<T> *tab, const LaneScratch<T, NT> &s,
                                int64_t game) {
     constexpr int E = 2 * NT + 1, PK = 2 * NT, SREC = 2 + 4 * E, NP = 2 * NT;
@@ -1271,6 +1275,12 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
 #pragma unroll 1
     for (; k < A.n_steps; ++k) {
         if (!(sa < wsc && sb < wsc)) break;  // undecided(), :57-60
+        if constexpr (kPolicy && !kRegs) {
+            T u[2 * NP];
+            surrogate_policy<T, NT>(P.d, A.pol, [&](int e, int c) { return s.F(S::SP + 4 * e + c); }, u);
+#pragma unroll
+            for (int c = 0; c < 2 * NP; ++c) s.F(S::CMD + c) = u[c];
+        } else
         if (fetch) {
             const int64_t ai = (A.synth || aidx < A.n_act) ? aidx : A.n_act - 1;
             if constexpr (kRegs) {

@@ -12,7 +12,7 @@
 
 namespace rgs {
 
-template <typename T, int NT, int THREADS>
+template <typename T, int NT, int THREADS, bool kPolicy = false>
 #ifndef RGS_LANE_MINBLOCKS
 #define RGS_LANE_MINBLOCKS 1
 #endif
@@ -42,7 +42,7 @@ __global__ void __launch_bounds__(THREADS, RGS_LANE_MINBLOCKS) rollout_lane_kern
 #else
     if ((int)threadIdx.x >= per_cta) return;
     for (int64_t game = (int64_t)blockIdx.x * per_cta + threadIdx.x; game < A.n_games; game += stride)
-        rollout_lane_game<T, NT>(P, A, tab, s, game);
+        rollout_lane_game<T, NT, kPolicy>(P, A, tab, s, game);
 #endif
 }
 
@@ -52,14 +52,14 @@ constexpr size_t lane_smem_bytes(int threads) {
            ((size_t)LaneScratch<T, NT>::NF * sizeof(T) + (size_t)LaneScratch<T, NT>::NI * sizeof(int)) * threads;
 }
 
-template <typename T, int NT, int kThreads>
+template <typename T, int NT, int kThreads, bool kPolicy = false>
 static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count,
                                      int lanes = kThreads) {
     size_t smem = lane_smem_bytes<T, NT>(lanes);
 #ifdef RGS_EXP_ONLY_2V2
     if (const char *pad = std::getenv("RGS_EXP_SMEM_PAD")) smem += (size_t)std::atoi(pad);  // occupancy sensitivity experiments
 #endif
-    auto kern = rollout_lane_kernel<T, NT, kThreads>;
+    auto kern = rollout_lane_kernel<T, NT, kThreads, kPolicy>;
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     int per_sm = 0;
@@ -86,6 +86,10 @@ static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cuda
     return launch_lane_sized<T, NT, RGS_LANE_THREADS>(P, A, stream, sm_count);
 #else
     constexpr int kBig = lane_smem_bytes<T, NT>(128) <= 110 * 1024 ? 128 : 64;
+    if (A.synth == 2) {  // closed loop on the on-device policy: instantiated for the reference's 2v2 only
+        if constexpr (NT == 2) return launch_lane_sized<T, NT, kBig, true>(P, A, stream, sm_count);
+        else return cudaErrorNotSupported;
+    }
     if (A.n_games < (int64_t)sm_count * kBig) {
         // games per one-warp CTA: aim at 7 warps per SM.  Measured on the 4096 x 50-step sampler tick
         // (profiles/r01_configs.json): 32 lanes 2.36 ms, 8 lanes 1.84, 4 lanes (6.9 warps/SM) 1.54, 2 lanes 1.87,

@@ -218,6 +218,28 @@ class BatchedGameSim:
                                                   float(u_max), int(n_steps), int(log_stride), traj_ptr, self._stream()))
         return traj
 
+    def run_policy(self, n_steps, log_stride=0, **policy):
+        """Closed loop on the on-device surrogate of the reference's baseline team (ClassicalTeam play logic and
+        targets, closed-form tracking law; `cbf=1` adds the CBF.py barrier filter): the commands are computed from
+        the state inside the kernel every step.  policy: kick_velocity, gain, input_limit, safety_radius,
+        barrier_gain, cbf, sweeps (include/rgs_capi.h rgs_policy).  FAST modes, 2 players per team."""
+        torch = self._torch
+        pol = _capi.RgsPolicy()
+        self._lib.rgs_default_policy(C.byref(pol))
+        for k, v in policy.items():
+            if k not in dict(_capi.RgsPolicy._fields_):
+                raise TypeError(f"unknown policy field {k!r}")
+            setattr(pol, k, v)
+        traj, traj_ptr = None, None
+        if log_stride:
+            np2 = 2 * self.n_team
+            traj = torch.empty((self.n_games, n_steps // log_stride, 1 + self.state_size + np2 * np2),
+                               dtype=torch.float64, device=self.device)
+            traj_ptr = traj.data_ptr()
+        _capi.check(self._lib.rgs_batch_run_policy(self._h, C.byref(pol), int(n_steps), int(log_stride), traj_ptr,
+                                                   self._stream()))
+        return traj
+
     # ---- read-back (device tensors) ----
     def _get(self, which):
         torch = self._torch

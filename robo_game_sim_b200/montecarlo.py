@@ -69,8 +69,11 @@ def monte_carlo_batched(mc_params, actions=None, policy=None, *, mode="fast", ra
     mc_params: the reference's parameter object (num_runs, T, dt, winning_score, x0_ball,
       noise_stdev, tau_puck, tau_player, player_mass, puck_mass, log_prefix).
     actions:  None, or an open-loop command tensor [n_act, 4, 2] shared by all runs / [runs, n_act, 4, 2].
-    policy:   None, or a callable  state[n,22] (device tensor) -> commands[n,4,2]; the batch is then
-              stepped one tick per call (closed loop, host in the loop like the reference).
+    policy:   None; a callable  state[n,22] (device tensor) -> commands[n,4,2] (the batch is then stepped one
+              tick per call: closed loop with the host in the loop, like the reference); or "classical" /
+              "classical+cbf" / a dict of rgs_policy fields: the ON-DEVICE surrogate of the reference's baseline
+              team for both sides (py/mc_example_1.py: ClassicalTeam vs ClassicalTeam, optionally behind the CBF
+              filter), the whole closed loop in one kernel launch (BatchedGameSim.run_policy).
     randomize: True draws the synthetic S0 puck state (and, with no actions/policy, S0 commands
               redrawn every `hold` steps) per GLOBAL run index; default: True iff neither actions
               nor policy is given (the reference MC with noise=0 is otherwise N copies of one game).
@@ -105,7 +108,14 @@ def monte_carlo_batched(mc_params, actions=None, policy=None, *, mode="fast", ra
         sim.reset(x0_ball=np.asarray(mc_params.x0_ball, dtype=np.float64))
     zero = torch.zeros((1, 4, 2), dtype=sim.action_dtype, device=sim.device)
     sim.run(zero, n_steps=1)  # priming step (py/MonteCarlo.py:33)
-    if policy is not None:
+    if isinstance(policy, (str, dict)):
+        fields = {"classical": {}, "classical+cbf": {"cbf": 1}}[policy] if isinstance(policy, str) else dict(policy)
+        fields.setdefault("input_limit", float(getattr(mc_params, "input_limit", 10.0)))
+        if fields.get("cbf"):
+            fields.setdefault("safety_radius", float(getattr(mc_params, "safety_radius", 0.4)))
+            fields.setdefault("barrier_gain", float(getattr(mc_params, "barrier_gain", 30.0)))
+        sim.run_policy(n_steps, **fields)
+    elif policy is not None:
         for _ in range(n_steps):
             cmd = policy(sim.state())
             sim.run(torch.as_tensor(cmd).reshape(count, 1, 4, 2), n_steps=1)

@@ -44,7 +44,10 @@ void run_lane(const rgs_params &p, const rgs::RunArgs &A, bool warp_sched = fals
     T fw[S::NF];
     int iw[S::NI];
     S s{fw, iw, 1};
-    if (warp_sched) rgs::rollout_lane_warp<T, NT>(P, A, tab.get(), s, 0, 1, 16);  // one lane walks all the games
+    if (A.synth == 2) {   // closed loop on the on-device surrogate policy (instantiated for 2v2, like the library)
+        if constexpr (NT == 2)
+            for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT, true>(P, A, tab.get(), s, g);
+    } else if (warp_sched) rgs::rollout_lane_warp<T, NT>(P, A, tab.get(), s, 0, 1, 16);  // one lane walks all the games
     else for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT>(P, A, tab.get(), s, g);
 }
 
@@ -112,6 +115,18 @@ void dispatch(const rgs_params &p, const rgs::RunArgs &A) {
 
 }  // namespace
 
+static rgs_policy g_policy;   // used by emu_rollout calls with synth == 2
+extern "C" void emu_set_policy(const rgs_policy *pol) { g_policy = *pol; }
+// the policy alone: commands [2 * 2n] of one game from its state record [2 + 4E] (fp64 arithmetic)
+extern "C" int emu_policy_commands(const rgs_params *p, const rgs_policy *pol, const double *state, double *u) {
+    if (p->players_per_team != 2) return -1;
+    const rgs::DevParams<double> d = rgs::make_dev_params<double>(*p);
+    const rgs::PolicyArgs a{pol->kick_velocity, pol->gain, pol->input_limit, pol->safety_radius, pol->barrier_gain, pol->cbf, pol->sweeps};
+    // state record: [TAS, TBS, puck, players...]; body index: players 0..3, puck 4
+    rgs::surrogate_policy<double, 2>(d, a, [&](int e, int c) { return state[2 + 4 * (e == 4 ? 0 : e + 1) + c]; }, u);
+    return 0;
+}
+
 extern "C" int emu_rollout(const rgs_params *p, int64_t n_games, double *state, double *clock, double *damage,
                            long long *events, const void *actions, int64_t n_act, int64_t hold, int64_t act_game_stride,
                            int64_t n_steps, int64_t log_stride, double *traj, int synth, uint64_t seed,
@@ -134,6 +149,11 @@ extern "C" int emu_rollout(const rgs_params *p, int64_t n_games, double *state, 
     A.first_game = first_game;
     A.step0 = step0;
     A.u_max = u_max;
+    if (synth == 2) {
+        if (p->players_per_team != 2 || p->mode == RGS_MODE_EXACT_F64) return -2;
+        A.pol = rgs::PolicyArgs{g_policy.kick_velocity, g_policy.gain, g_policy.input_limit, g_policy.safety_radius,
+                                g_policy.barrier_gain, g_policy.cbf, g_policy.sweeps};
+    }
     switch (p->players_per_team) {
     case 1: dispatch<1>(*p, A); break;
     case 2: dispatch<2>(*p, A); break;

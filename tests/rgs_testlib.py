@@ -40,6 +40,18 @@ class RgsParams(C.Structure):
                 ("goal_height", C.c_double), ("mode", C.c_int32), ("reserved", C.c_int32)]
 
 
+class RgsPolicy(C.Structure):
+    _fields_ = [("kick_velocity", C.c_double), ("gain", C.c_double), ("input_limit", C.c_double),
+                ("safety_radius", C.c_double), ("barrier_gain", C.c_double), ("cbf", C.c_int32), ("sweeps", C.c_int32)]
+
+
+def default_policy(**kw):
+    """rgs_default_policy of include/rgs_capi.h."""
+    d = dict(kick_velocity=4.0, gain=4.0, input_limit=10.0, safety_radius=0.4, barrier_gain=30.0, cbf=0, sweeps=8)
+    d.update(kw)
+    return d
+
+
 def _ptr(a, ct=C.c_double):
     return None if a is None else a.ctypes.data_as(C.POINTER(ct))
 
@@ -187,8 +199,21 @@ def oracle_rollout_reltime(pd, state, actions, n_steps, hold=1, threads=8):
     return dict(state=st, damage=dm, events=ev)
 
 
-def emu_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, events=None, log_stride=0, synth=None):
-    """The product's kernel body stepped on the CPU warp emulator (one warp, games in sequence)."""
+def emu_policy_commands(pd, pol, state):
+    """Commands [n, 4, 2] of the on-device surrogate policy for state records [n, 22] (emulator build, fp64)."""
+    lib = emu_lib()
+    p, q = rgs_params(pd), RgsPolicy(**pol)
+    state = np.ascontiguousarray(state, dtype=np.float64)
+    u = np.zeros((state.shape[0], 8))
+    for g in range(state.shape[0]):
+        assert lib.emu_policy_commands(C.byref(p), C.byref(q), _ptr(state[g]), _ptr(u[g])) == 0
+    return u.reshape(-1, 4, 2)
+
+
+def emu_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, events=None, log_stride=0, synth=None,
+                policy=None):
+    """The product's kernel body stepped on the CPU warp emulator (one warp, games in sequence).
+    policy: a default_policy() dict = closed loop on the on-device surrogate policy (actions ignored)."""
     lib = emu_lib()
     p = rgs_params(pd)
     n = state.shape[0]
@@ -200,7 +225,12 @@ def emu_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, events
     traj = None
     if log_stride:
         traj = np.zeros((n, n_steps // log_stride, 1 + state.shape[1] + 4 * nt * nt))
-    if synth is not None:
+    if policy is not None:
+        q = RgsPolicy(**policy)
+        lib.emu_set_policy(C.byref(q))
+        rc = lib.emu_rollout(C.byref(p), n, _ptr(state), _ptr(t), _ptr(damage), _ptr(events, C.c_int64), None, 1, 1,
+                             0, n_steps, log_stride, _ptr(traj), 2, 0, 0, 0, 0.0)
+    elif synth is not None:
         seed, first_game, step0, u_max = synth
         rc = lib.emu_rollout(C.byref(p), n, _ptr(state), _ptr(t), _ptr(damage), _ptr(events, C.c_int64), None, 1, hold,
                              0, n_steps, log_stride, _ptr(traj), 1, seed, first_game, step0, u_max)

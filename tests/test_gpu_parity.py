@@ -383,3 +383,56 @@ def test_ragged_batch_sizes_and_cta_size_switch(rgs, n):
         o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), acts, steps, hold)
         _, x = _gpu_rollout(rgs, "exact", pd, x0, acts, steps, hold)
         _assert_bit_exact(o, x)
+
+
+# ------------------------------------------------------------------ §8(f) rank 4: on-device surrogate policy
+def test_on_device_policy_closed_loop(rgs, tmp_path):
+    """The closed loop runs inside the K2 kernel.  Without the barrier filter the policy is add / mul / div / sqrt
+    only: the GPU must equal the emulator build of the same source bit for bit (fp32).  With the filter (one expf per
+    approaching pair, not bit-identical between CUDA and glibc) the first steps agree to rounding and the behaviour
+    agrees: the filter removes the player-player impacts.  The Monte Carlo harness drives it with policy="classical"."""
+    n, steps = 3000, 200
+    pd = tl.default_params(winning_score=3, mode=tl.MODE_FAST_F32)
+    x0, _ = tl.synth_inputs(31, 0, n, 2, 1)
+    kw = {k: pd[k] for k in ("dt", "winning_score", "tau_puck", "tau_player", "player_mass", "puck_mass")}
+    sim = rgs.BatchedGameSim(n, mode="fast", **kw)
+
+    def gpu(n_steps, **pol):
+        sim.reset(x0_ball=torch.from_numpy(x0).cuda())
+        traj = sim.run_policy(n_steps, log_stride=n_steps, **pol)
+        return dict(state=sim.state().cpu().numpy(), events=sim.events().cpu().numpy(), t=sim.time().cpu().numpy(),
+                    damage=sim.damage().cpu().numpy().reshape(n, -1), traj=traj.cpu().numpy())
+
+    s0 = tl.oracle_reset(tl.default_params(), x0)
+    g = gpu(steps)
+    sub = slice(0, 400)
+    e = tl.emu_rollout(pd, s0[sub], None, steps, policy=tl.default_policy())
+    assert np.array_equal(g["state"][sub], e["state"]) and np.array_equal(g["events"][sub], e["events"])
+    assert np.array_equal(g["damage"][sub], e["damage"]) and np.array_equal(g["t"][sub], e["t"])
+    assert np.array_equal(g["traj"][:, 0, 1:23], g["state"])          # the strided log holds the final state
+    assert g["state"][:, :2].sum() > 100 and g["events"][:, 7].sum() > 10 * n   # games are played: goals, kicks
+    # barrier filter
+    g3 = gpu(3, cbf=1)
+    e3 = tl.emu_rollout(pd, s0[sub], None, 3, policy=tl.default_policy(cbf=1))
+    same = (g3["events"][sub, 2:8] == e3["events"][:, 2:8]).all(axis=1)
+    assert same.mean() > 0.99 and np.abs(g3["state"][sub][same] - e3["state"][same]).max() < 1e-3
+    gs = gpu(steps, cbf=1)
+    assert gs["events"][:, 6].sum() < 0.1 * g["events"][:, 6].sum()
+    # error behaviour: exact mode and other team sizes are refused, loudly
+    with pytest.raises(RuntimeError, match="on-device policy"):
+        rgs.BatchedGameSim(8, mode="exact").reset(x0_ball=np.zeros(4)).run_policy(5)
+    with pytest.raises(RuntimeError, match="on-device policy"):
+        rgs.BatchedGameSim(8, mode="fast", players_per_team=3).reset(x0_ball=np.zeros(4)).run_policy(5)
+    with pytest.raises(TypeError):
+        sim.run_policy(5, kick=1.0)
+    # the Monte Carlo harness, both teams on the device-side baseline policy (py/mc_example_1.py)
+    import types
+
+    mc = types.SimpleNamespace(num_runs=20000, T=10.0, dt=0.05, winning_score=4, x0_ball=np.array([-1.0, 0, 0, 0]),
+                               noise_stdev=0.0, tau_puck=0.1, tau_player=0.5, player_mass=1.0, puck_mass=0.5,
+                               log_prefix=str(tmp_path / "mcp"))
+    free = rgs.monte_carlo_batched(mc, policy="classical", randomize=True, seed=5)
+    safe = rgs.monte_carlo_batched(mc, policy="classical+cbf", randomize=True, seed=5)
+    assert free["games"] == 20000 and free["n_steps"] == 200 and free["goals_a"] + free["goals_b"] > 500
+    assert 0.7 < free["goals_a"] / free["goals_b"] < 1.4            # mirror-symmetric teams, symmetric S0 pucks
+    assert safe["player_player"] < 0.1 * free["player_player"]
