@@ -132,6 +132,9 @@ typedef struct rgs_policy {
     double barrier_gain;   /* 30    mc_example_1.py:36 */
     int32_t cbf;           /* 0 = nominal commands, 1 = barrier filter on (mc_example_1.py:45) */
     int32_t sweeps;        /* Hildreth sweeps of the filter, e.g. 8 */
+    int32_t kind;          /* 0 = ClassicalTeam play logic and targets; 1 = DMPCTeam / DMPCPlayer play logic and
+                              targets x_des (py/src/DMPCTeam.py:78-93, py/src/DMPCPlayer.py:27-57; A1 / B1 attacker) */
+    int32_t reserved;
 } rgs_policy;
 void rgs_default_policy(rgs_policy *pol);
 int rgs_batch_run_policy(rgs_batch *b, const rgs_policy *pol, int64_t n_steps, int64_t log_stride, double *d_traj,

@@ -31,7 +31,8 @@ class RgsParams(C.Structure):
 class RgsPolicy(C.Structure):
     """rgs_policy of include/rgs_capi.h (defaults: rgs_default_policy)."""
     _fields_ = [("kick_velocity", C.c_double), ("gain", C.c_double), ("input_limit", C.c_double),
-                ("safety_radius", C.c_double), ("barrier_gain", C.c_double), ("cbf", C.c_int32), ("sweeps", C.c_int32)]
+                ("safety_radius", C.c_double), ("barrier_gain", C.c_double), ("cbf", C.c_int32), ("sweeps", C.c_int32),
+                ("kind", C.c_int32), ("reserved", C.c_int32)]
 
 
 # every symbol include/rgs_capi.h declares: (restype, argtypes)

@@ -124,7 +124,7 @@ int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64
         if (b->p.mode == RGS_MODE_EXACT_F64 || b->n_team != 2 || b->warp_k2 || !b->lane_k2)
             return fail(RGS_EUNSUPPORTED, "the on-device policy runs in the FAST modes of the lane kernel with players_per_team == 2");
         A.pol = rgs::PolicyArgs{b->pol.kick_velocity, b->pol.gain, b->pol.input_limit, b->pol.safety_radius,
-                                b->pol.barrier_gain, b->pol.cbf, b->pol.sweeps};
+                                b->pol.barrier_gain, b->pol.cbf, b->pol.sweeps, b->pol.kind};
     }
     cudaError_t e;
     switch (b->p.mode) {
@@ -347,6 +347,8 @@ void rgs_default_policy(rgs_policy *pol) {
     pol->barrier_gain = 30.0;
     pol->cbf = 0;
     pol->sweeps = 8;
+    pol->kind = 0;
+    pol->reserved = 0;
 }
 
 int rgs_batch_run_policy(rgs_batch *b, const rgs_policy *pol, int64_t n_steps, int64_t log_stride, double *d_traj,
@@ -354,6 +356,7 @@ int rgs_batch_run_policy(rgs_batch *b, const rgs_policy *pol, int64_t n_steps, i
     int rc = check_run_args(b, 1, 1, n_steps, log_stride, d_traj);
     if (rc != RGS_OK) return rc;
     if (!pol) return fail(RGS_EINVAL, "pol is NULL");
+    if (pol->kind != 0 && pol->kind != 1) return fail(RGS_EINVAL, "policy: kind must be 0 (classical) or 1 (dmpc)");
     if (!(pol->input_limit > 0.0) || !(pol->gain >= 0.0)) return fail(RGS_EINVAL, "policy: input_limit must be > 0 and gain >= 0");
     if (pol->cbf && (pol->sweeps < 1 || !(pol->barrier_gain > 0.0) || !(pol->safety_radius >= 2.0 * b->p.player_radius)))
         return fail(RGS_EINVAL, "policy: the barrier filter needs sweeps >= 1, barrier_gain > 0 and safety_radius >= 2 player_radius (CBF.py:29-30)");

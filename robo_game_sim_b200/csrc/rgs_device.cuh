@@ -58,7 +58,7 @@ struct DevParams {
 // on-device surrogate policy (rgs_policy.cuh); mirrors rgs_policy of include/rgs_capi.h
 struct PolicyArgs {
     double kick_velocity, gain, input_limit, safety_radius, barrier_gain;
-    int cbf, sweeps;
+    int cbf, sweeps, kind;
 };
 
 struct RunArgs {

@@ -17,6 +17,9 @@
 //   * targets: kick = touch the puck from behind along the shooting direction with the kick velocity
 //     (get_final_state_for_kick, py/src/ClassicalPlayer.py:232-237; get_shoot_direction :239-244; defend_kick
 //     :190-207), defend = half way between the own goal and the puck at rest (defend :209-222);
+//   * kind = 1: the DMPC teams' play selection and target states x_des instead (DMPCTeam.execute,
+//     py/src/DMPCTeam.py:78-93; DMPCPlayer.get_action, py/src/DMPCPlayer.py:27-57); the SNOPT collocation
+//     (py/src/DMPC.py:16-54) that steers towards x_des is replaced by the same tracking law;
 //   * surrogate tracking law (ours): u = clamp(v_f + gain (p_f - p), +-input_limit) on the first-order velocity plant.
 // Optional safety filter: the reference's centralised control-barrier constraints for the damped double
 // integrator (py/src/CBF.py:36-76: one half-space in u_i - u_j per approaching player pair, closed form) with
@@ -62,11 +65,26 @@ RGS_DEV void surrogate_policy(const DevParams<T> &d, const PolicyArgs &pol, Stat
 #pragma unroll
         for (int q = 0; q < NT; ++q) {
             const int me = team * NT + q;
-            int task;  // 0 defend, 1 kick at the goal, 2 clear
-            if (!defense) task = (q == 0 && f * px >= T(0)) ? 0 : 1;
+            int task;  // 0 defend, 1 kick at the goal, 2 clear, 3 / 4 DMPC hit with 1 x / 2 x the hit speed
+            if (pol.kind == 1) {
+                // DMPCTeam.execute :78-88 (thresholds arena_x - arena_x/4 and arena_x - arena_x/2 on |x| <= arena_x/2:
+                // as written in the reference both are out of reach, the team always plays OFFENSE)
+                const T ax = d.half_x + d.half_x;
+                const bool dmpc_def = (f * px > ax - ax * T(0.25)) ||
+                                      ((f * px > ax - ax * T(0.5)) && (f * pvx > ax / T(10)));
+                const bool attacker = q != 1;     // A1 / B1 (get_action :27-57); the second player is the defender
+                if (!dmpc_def) task = attacker ? 3 : (f * px > T(0) ? 0 : 3);
+                else task = attacker ? 4 : 0;
+            } else if (!defense) task = (q == 0 && f * px >= T(0)) ? 0 : 1;
             else task = q == 0 ? 0 : 2;
             T pfx, pfy, vfx, vfy;
-            if (task == 0) {
+            if (task >= 3) {   // x_des = [puck, scale v_hit (goal - puck) / |goal - puck|]
+                T hx = goal_x - px, hy = T(0) - py;
+                if (sn > T(0)) { hx = hx / sn; hy = hy / sn; }
+                const T sc = task == 4 ? T(2) * kv : kv;
+                pfx = px; pfy = py;
+                vfx = sc * hx; vfy = sc * hy;
+            } else if (task == 0) {
                 pfx = home_x + T(0.5) * (px - home_x); pfy = T(0.5) * py;
                 vfx = T(0); vfy = T(0);
             } else if (task == 1) {

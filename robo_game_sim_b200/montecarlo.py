@@ -71,7 +71,7 @@ def monte_carlo_batched(mc_params, actions=None, policy=None, *, mode="fast", ra
     actions:  None, or an open-loop command tensor [n_act, 4, 2] shared by all runs / [runs, n_act, 4, 2].
     policy:   None; a callable  state[n,22] (device tensor) -> commands[n,4,2] (the batch is then stepped one
               tick per call: closed loop with the host in the loop, like the reference); or "classical" /
-              "classical+cbf" / a dict of rgs_policy fields: the ON-DEVICE surrogate of the reference's baseline
+              "classical+cbf" / "dmpc" / "dmpc+cbf" / a dict of rgs_policy fields: the ON-DEVICE surrogate of the reference's baseline
               team for both sides (py/mc_example_1.py: ClassicalTeam vs ClassicalTeam, optionally behind the CBF
               filter), the whole closed loop in one kernel launch (BatchedGameSim.run_policy).
     randomize: True draws the synthetic S0 puck state (and, with no actions/policy, S0 commands
@@ -109,7 +109,8 @@ def monte_carlo_batched(mc_params, actions=None, policy=None, *, mode="fast", ra
     zero = torch.zeros((1, 4, 2), dtype=sim.action_dtype, device=sim.device)
     sim.run(zero, n_steps=1)  # priming step (py/MonteCarlo.py:33)
     if isinstance(policy, (str, dict)):
-        fields = {"classical": {}, "classical+cbf": {"cbf": 1}}[policy] if isinstance(policy, str) else dict(policy)
+        named = {"classical": {}, "classical+cbf": {"cbf": 1}, "dmpc": {"kind": 1}, "dmpc+cbf": {"kind": 1, "cbf": 1}}
+        fields = dict(named[policy]) if isinstance(policy, str) else dict(policy)
         fields.setdefault("input_limit", float(getattr(mc_params, "input_limit", 10.0)))
         if fields.get("cbf"):
             fields.setdefault("safety_radius", float(getattr(mc_params, "safety_radius", 0.4)))

@@ -121,7 +121,7 @@ extern "C" void emu_set_policy(const rgs_policy *pol) { g_policy = *pol; }
 extern "C" int emu_policy_commands(const rgs_params *p, const rgs_policy *pol, const double *state, double *u) {
     if (p->players_per_team != 2) return -1;
     const rgs::DevParams<double> d = rgs::make_dev_params<double>(*p);
-    const rgs::PolicyArgs a{pol->kick_velocity, pol->gain, pol->input_limit, pol->safety_radius, pol->barrier_gain, pol->cbf, pol->sweeps};
+    const rgs::PolicyArgs a{pol->kick_velocity, pol->gain, pol->input_limit, pol->safety_radius, pol->barrier_gain, pol->cbf, pol->sweeps, pol->kind};
     // state record: [TAS, TBS, puck, players...]; body index: players 0..3, puck 4
     rgs::surrogate_policy<double, 2>(d, a, [&](int e, int c) { return state[2 + 4 * (e == 4 ? 0 : e + 1) + c]; }, u);
     return 0;
@@ -152,7 +152,7 @@ extern "C" int emu_rollout(const rgs_params *p, int64_t n_games, double *state, 
     if (synth == 2) {
         if (p->players_per_team != 2 || p->mode == RGS_MODE_EXACT_F64) return -2;
         A.pol = rgs::PolicyArgs{g_policy.kick_velocity, g_policy.gain, g_policy.input_limit, g_policy.safety_radius,
-                                g_policy.barrier_gain, g_policy.cbf, g_policy.sweeps};
+                                g_policy.barrier_gain, g_policy.cbf, g_policy.sweeps, g_policy.kind};
     }
     switch (p->players_per_team) {
     case 1: dispatch<1>(*p, A); break;

@@ -42,12 +42,13 @@ class RgsParams(C.Structure):
 
 class RgsPolicy(C.Structure):
     _fields_ = [("kick_velocity", C.c_double), ("gain", C.c_double), ("input_limit", C.c_double),
-                ("safety_radius", C.c_double), ("barrier_gain", C.c_double), ("cbf", C.c_int32), ("sweeps", C.c_int32)]
+                ("safety_radius", C.c_double), ("barrier_gain", C.c_double), ("cbf", C.c_int32), ("sweeps", C.c_int32),
+                ("kind", C.c_int32), ("reserved", C.c_int32)]
 
 
 def default_policy(**kw):
     """rgs_default_policy of include/rgs_capi.h."""
-    d = dict(kick_velocity=4.0, gain=4.0, input_limit=10.0, safety_radius=0.4, barrier_gain=30.0, cbf=0, sweeps=8)
+    d = dict(kick_velocity=4.0, gain=4.0, input_limit=10.0, safety_radius=0.4, barrier_gain=30.0, cbf=0, sweeps=8, kind=0, reserved=0)
     d.update(kw)
     return d
 

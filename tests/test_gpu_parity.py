@@ -411,6 +411,10 @@ def test_on_device_policy_closed_loop(rgs, tmp_path):
     assert np.array_equal(g["damage"][sub], e["damage"]) and np.array_equal(g["t"][sub], e["t"])
     assert np.array_equal(g["traj"][:, 0, 1:23], g["state"])          # the strided log holds the final state
     assert g["state"][:, :2].sum() > 100 and g["events"][:, 7].sum() > 10 * n   # games are played: goals, kicks
+    gd = gpu(steps, kind=1)                                           # DMPC play logic and targets
+    ed = tl.emu_rollout(pd, s0[sub], None, steps, policy=tl.default_policy(kind=1))
+    assert np.array_equal(gd["state"][sub], ed["state"]) and np.array_equal(gd["events"][sub], ed["events"])
+    assert not np.array_equal(gd["state"], g["state"])
     # barrier filter
     g3 = gpu(3, cbf=1)
     e3 = tl.emu_rollout(pd, s0[sub], None, 3, policy=tl.default_policy(cbf=1))

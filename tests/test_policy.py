@@ -168,3 +168,30 @@ def test_policy_games_are_played_out():
     assert goals[0] >= 5 and goals[1] >= 5 and goals.sum() >= 20                 # both sides score
     pp_free, pp_safe = free["events"][:, tl.EV["PLAYER_PLAYER"]].sum(), safe["events"][:, tl.EV["PLAYER_PLAYER"]].sum()
     assert pp_free > 1000 and pp_safe < 0.1 * pp_free
+
+
+def test_dmpc_kind_follows_the_dmpc_play_logic_and_targets():
+    """kind = 1: play and x_des of DMPCTeam.execute / DMPCPlayer.get_action -- restated on the host in
+    robo_game_sim_b200/sampler.py (dmpc_play, dmpc_target), which test_capi_and_host.py checks against the reference
+    text -- with the surrogate tracking law on top."""
+    from robo_game_sim_b200 import sampler as sp
+
+    pd, pol = tl.default_params(mode=tl.MODE_FAST_F64), tl.default_policy(kind=1, gain=3.0)
+    states = random_states(300, 4)
+    states[:40, 2] = np.linspace(-4.9, 4.9, 40)
+    got = tl.emu_policy_commands(pd, pol, states)
+    for s, u in zip(states, got):
+        for team, field in ((0, -1), (1, 1)):
+            play = sp.dmpc_play(s, field)
+            assert play == sp.OFFENSE      # the reference's thresholds are out of the arena's reach (DMPCTeam.py:81-84)
+            goal, home = [-field * 5.0, 0.0], [field * 5.0, 0.0]
+            for q, pid in ((0, sp.ATTACKER), (1, sp.DEFENDER)):
+                xd = sp.dmpc_target(s, play, pid, field, goal, home, v_hit=pol["kick_velocity"])
+                me = s[6 + 4 * (2 * team + q):8 + 4 * (2 * team + q)]
+                want = np.clip(xd[2:] + pol["gain"] * (xd[:2] - me), -pol["input_limit"], pol["input_limit"])
+                assert np.abs(u[2 * team + q] - want).max() <= 1e-12
+    # and it plays: closed loop with the barrier filter on, fp32
+    x0, _ = tl.synth_inputs(23, 0, 100, 2, 1)
+    r = tl.emu_rollout(dict(pd, mode=tl.MODE_FAST_F32, winning_score=3), tl.oracle_reset(tl.default_params(), x0), None, 200,
+                       policy=tl.default_policy(kind=1, cbf=1))
+    assert r["events"][:, tl.EV["PLAYER_PUCK"]].sum() > 100 and r["state"][:, :2].sum() >= 5
