@@ -70,11 +70,13 @@ struct rgs_batch {
     rgs_params p{};
     int n_team = 2, E = 5, srec = 22, dmg_rec = 16;
     rgs_policy pol{};      // the on-device policy of the current rgs_batch_run_policy call
-    bool warp_k2 = false;  // RGS_K2_WARP=1: the superseded warp-per-game throughput kernel (A/B measurements only)
-    bool lane_k2 = true;   // RGS_K2_LANE=0: the phased block kernel (rgs_phase.cuh) instead of one lane per game (A/B; teams <= 3)
     double *state = nullptr, *clock = nullptr, *damage = nullptr;
     long long *events = nullptr, *stats = nullptr;
     unsigned long long *cost_scratch = nullptr;  // K3 arg-min partials, allocated on first use
+    // K2 per-lane scratch (correctOverlap tracks, rgs_lane.cuh), one per stream a rollout can be in flight on:
+    // [0] the caller's stream, [1], [2] the two private streams of rgs_batch_run_host; allocated on first use
+    void *lane_scratch[3] = {nullptr, nullptr, nullptr};
+    size_t lane_scratch_bytes = 0;
     // staging for rgs_batch_run_host
     void *stage_actions = nullptr;
     size_t stage_actions_bytes = 0;
@@ -98,7 +100,7 @@ struct DeviceGuard {
 // one fused launch over games [g0, g1) of the batch
 int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64_t n_act, int64_t hold,
               int64_t act_game_stride, int64_t n_steps, int64_t log_stride, double *d_traj, int synth, uint64_t seed,
-              int64_t first_game, int64_t step0, double u_max, cudaStream_t stream) {
+              int64_t first_game, int64_t step0, double u_max, cudaStream_t stream, int slot = 0) {
     if (g1 <= g0 || n_steps == 0) return RGS_OK;
     rgs::RunArgs A{};
     const int np = 2 * b->n_team;
@@ -121,10 +123,25 @@ int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64
     A.step0 = step0;
     A.u_max = u_max;
     if (synth == 2) {
-        if (b->p.mode == RGS_MODE_EXACT_F64 || b->n_team != 2 || b->warp_k2 || !b->lane_k2)
+        if (b->p.mode == RGS_MODE_EXACT_F64 || b->n_team != 2)
             return fail(RGS_EUNSUPPORTED, "the on-device policy runs in the FAST modes of the lane kernel with players_per_team == 2");
         A.pol = rgs::PolicyArgs{b->pol.kick_velocity, b->pol.gain, b->pol.input_limit, b->pol.safety_radius,
                                 b->pol.barrier_gain, b->pol.cbf, b->pol.sweeps, b->pol.kind};
+    }
+    if (b->p.mode != RGS_MODE_EXACT_F64) {
+        if (b->lane_scratch_bytes == 0) {
+            cudaError_t qe = rgs::lane_scratch_bytes(b->n_team, b->p.mode == RGS_MODE_FAST_F64, b->sm_count, &b->lane_scratch_bytes);
+            if (qe != cudaSuccess) return cuda_fail(qe, "lane scratch size query");
+        }
+        if (!b->lane_scratch[slot]) {
+            cudaError_t me = cudaMalloc(&b->lane_scratch[slot], b->lane_scratch_bytes);
+            if (me != cudaSuccess) {
+                cudaGetLastError();
+                return fail(RGS_ENOMEM, "lane scratch of %zu bytes: %s", b->lane_scratch_bytes, cudaGetErrorString(me));
+            }
+        }
+        A.lane_scratch = b->lane_scratch[slot];
+        A.lane_scratch_bytes = b->lane_scratch_bytes;
     }
     cudaError_t e;
     switch (b->p.mode) {
@@ -132,14 +149,10 @@ int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64
         e = rgs::launch_rollout_exact(b->n_team, rgs::make_dev_params<double>(b->p), A, stream, b->sm_count);
         break;
     case RGS_MODE_FAST_F32:
-        e = b->warp_k2 ? rgs::launch_rollout_fast_f32(b->n_team, b->p, A, stream, b->sm_count)
-            : (b->lane_k2 || b->n_team > 3) ? rgs::launch_rollout_lane_f32(b->n_team, b->p, A, stream, b->sm_count)
-                                            : rgs::launch_rollout_phase_f32(b->n_team, b->p, A, stream, b->sm_count);
+        e = rgs::launch_rollout_lane_f32(b->n_team, b->p, A, stream, b->sm_count);
         break;
     default:
-        e = b->warp_k2 ? rgs::launch_rollout_fast_f64(b->n_team, b->p, A, stream, b->sm_count)
-            : (b->lane_k2 || b->n_team > 3) ? rgs::launch_rollout_lane_f64(b->n_team, b->p, A, stream, b->sm_count)
-                                            : rgs::launch_rollout_phase_f64(b->n_team, b->p, A, stream, b->sm_count);
+        e = rgs::launch_rollout_lane_f64(b->n_team, b->p, A, stream, b->sm_count);
         break;
     }
     if (e != cudaSuccess) return cuda_fail(e, "rollout kernel launch");
@@ -218,12 +231,6 @@ int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_par
     b->E = 2 * b->n_team + 1;
     b->srec = 2 + 4 * b->E;
     b->dmg_rec = 4 * b->n_team * b->n_team;
-    {
-        const char *w = std::getenv("RGS_K2_WARP");
-        b->warp_k2 = w && w[0] == '1';
-        const char *l = std::getenv("RGS_K2_LANE");
-        b->lane_k2 = !(l && l[0] == '0');
-    }
     cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
     const size_t n = (size_t)(n_games > 0 ? n_games : 1);
     cudaError_t err = cudaSuccess;
@@ -258,6 +265,7 @@ int rgs_batch_destroy(rgs_batch *b) {
     cudaFree(b->events);
     cudaFree(b->stats);
     cudaFree(b->cost_scratch);
+    for (int k = 0; k < 3; ++k) cudaFree(b->lane_scratch[k]);
     cudaFree(b->stage_actions);
     cudaFree(b->stage_x0);
     for (int k = 0; k < 2; ++k) {
@@ -463,7 +471,7 @@ int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_acti
                                           b->events + g0 * RGS_N_EVENTS, s);
         if (e != cudaSuccess) return cuda_fail(e, "reset kernel launch");
         g_launches.fetch_add(1);
-        rc = run_range(b, g0, g1, b->stage_actions, n_act, hold, arec, n_steps, 0, nullptr, 0, 0, 0, 0, 0.0, s);
+        rc = run_range(b, g0, g1, b->stage_actions, n_act, hold, arec, n_steps, 0, nullptr, 0, 0, 0, 0, 0.0, s, 1 + (int)(c & 1));
         if (rc != RGS_OK) return rc;
         if (h_state)
             RGS_CUDA(cudaMemcpyAsync(h_state + g0 * b->srec, b->state + g0 * b->srec, (size_t)ng * b->srec * sizeof(double),

@@ -77,6 +77,9 @@ struct RunArgs {
     int64_t first_game, step0;
     double u_max;
     PolicyArgs pol;
+    // K2 lane kernel: per-resident-lane global scratch (correctOverlap tracks + jam snapshot, rgs_lane.cuh)
+    void *lane_scratch;
+    size_t lane_scratch_bytes;
 };
 
 // ---- Philox4x32-10 (Salmon et al. 2011), counter-based: keyed by (seed, game, action index) ----

@@ -1,5 +1,4 @@
-// rgs_kernels.h -- launchers of the sm_100a kernels (one translation unit per kernel family so the
-// exact kernel can be built with -fmad=false while the throughput kernel keeps FMA contraction).
+// rgs_kernels.h -- launchers of the sm_100a kernels (one translation unit per kernel family).
 #pragma once
 #include <cuda_runtime.h>
 
@@ -11,20 +10,12 @@ namespace rgs {
 cudaError_t launch_rollout_exact(int n_team, const DevParams<double> &P, const RunArgs &A, cudaStream_t stream,
                                  int sm_count);
 
-// K2: exact affine sub-step map, step-relative time, FMA; fp32 (throughput) and fp64 (validation
-// of the formulation against the oracle) instantiations (rgs_fast_kernel.cu)
-cudaError_t launch_rollout_fast_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
-cudaError_t launch_rollout_fast_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
-
-// K2, one lane per game (rgs_lane_kernel.cu): the throughput kernel the FAST modes run
+// K2, one lane per game (rgs_lane_kernel.cu): the throughput kernel the FAST modes run; fp32 (throughput) and fp64
+// (validation of the formulation against the oracle) instantiations.  A.lane_scratch must point at
+// lane_scratch_bytes() bytes of device memory that no other launch in flight uses.
 cudaError_t launch_rollout_lane_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 cudaError_t launch_rollout_lane_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
-
-// K2, phased block kernel (rgs_phase_kernel.cu): same arithmetic and bit-identical results, narrow-phase items and
-// popped events compacted across the CTA; 37 % fewer instructions but barrier-latency-bound (1.50e9 vs 2.16e9
-// game-steps/s on B200), selected with RGS_K2_LANE=0 for teams of up to 3
-cudaError_t launch_rollout_phase_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
-cudaError_t launch_rollout_phase_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
+cudaError_t lane_scratch_bytes(int n_team, int fp64, int sm_count, size_t *bytes);
 
 // K4: per-batch statistics vector int64[RGS_N_STATS] (rgs_aux_kernels.cu)
 cudaError_t launch_stats(int n_team, int64_t n_games, const double *state, const long long *events, int winning_score,

@@ -32,9 +32,11 @@
 //   * events are resolved exactly like K2's warp formulation did (rgs_fast.cuh history): advance
 //     to the impact time with the RK4 polynomial, 1.01 overlap push, elastic impulse, damage,
 //     advance to the next column, correctOverlap on every later column.
-// Deviation kept on purpose (documented in DESIGN.md): only the LAST correctOverlap offset of a
-// body is tracked per column; a third body that re-scans against columns between two earlier
-// offsets of the same step sees the later offset early (affects jammed multi-contact steps only).
+// correctOverlap offsets are CUMULATIVE in the reference (a column is integrated from the corrected previous
+// column, :292-297, :336-340), so a body pressed against a wall or another body is corrected on every column.  The
+// segment keeps the total offset (in force from the column of the last fix on), the column of the first fix (no
+// offset before it) and, only when a segment has been fixed more than once, the cumulative offset of the columns in
+// between in a per-lane TRACK in global memory (LaneScratch::trk; lane-interleaved, touched by such bodies only).
 //
 // Everything is plain scalar C++ over a per-game scratch record, so tests/emu compiles the same
 // source with g++ (no warp emulation needed).  All fused multiply-adds are spelled out (fm()).
@@ -52,6 +54,8 @@
 
 namespace rgs {
 
+constexpr int kJamLog = 6;   // longest period of a jammed event loop that is fast-forwarded (LaneGame::JamSnap)
+
 // per-game scratch record: word w of game slot s lives at base[w * stride + s] (bank = lane)
 template <typename T, int NT>
 struct LaneScratch {
@@ -60,18 +64,28 @@ struct LaneScratch {
     static constexpr int SP = 0;         // [4e+c] state at the segment start column
     static constexpr int CMD = 4 * E;    // [2e+a] commanded velocity (puck: 0)
     static constexpr int PRV = 6 * E;    // [4e+c] state at the column before the segment start
-    static constexpr int OFF = 10 * E;   // [4e+{0,1}] total correctOverlap offset, [4e+{2,3}] offset before the last fix
-    static constexpr int BB = 14 * E;    // [4e+{0..3}] bounding interval lo_x, hi_x, lo_y, hi_y of the segment
-    static constexpr int QT = 18 * E;    // [e] queued / candidate event time of owner e
-    static constexpr int NF = 19 * E;
+    static constexpr int OFF = 10 * E;   // [2e+a] total correctOverlap offset of the segment (in force from column FL on)
+    static constexpr int BB = 12 * E;    // [4e+{0..3}] bounding interval lo_x, hi_x, lo_y, hi_y of the segment
+    static constexpr int QT = 16 * E;    // [e] queued / candidate event time of owner e
+    static constexpr int NF = 17 * E;
     // int words
     static constexpr int CS = 0;         // [e] segment start column
     static constexpr int FL = E;         // [e] column of the last correctOverlap fix (= CS when none)
     static constexpr int QI = 2 * E;     // [e] (seq << 12) | (col << 6)... see q_pack
-    static constexpr int NI = 3 * E;
+    static constexpr int FF = 3 * E;     // [e] column of the first correctOverlap fix (= CS when none)
+    static constexpr int TS = 4 * E;     // [e] checksum of the track words written for this segment (jam detection)
+    static constexpr int EVC = 5 * E;    // [k] event counters of this launch (RGS_EV_* order; [RGS_EV_HASH], [16] = hash lo, hi)
+    static constexpr int NI = 5 * E + 17;
+    // per-lane global scratch area, in T-sized words: the tracks, then the jam snapshot (LaneGame::JamSnap)
+    static constexpr int TRK_WORDS = 2 * E * kCols;
+    static constexpr int JAM_F = QT + E, JAM_I = 5 * E + 17 + 3 * kJamLog;
+    static constexpr int SCR_WORDS = TRK_WORDS + JAM_F + JAM_I;
     T *f;
     int *i;
     int stride;
+    T *trk;        // cumulative offset of column c, axis a of body e at trk[((e * kCols + c) * 2 + a) * tstride]
+    int tstride;
+    RGS_DEV T &TR(int e, int c, int a) const { return trk[(size_t)((e * kCols + c) * 2 + a) * tstride]; }
     RGS_DEV T &F(int w) const { return f[w * stride]; }
     RGS_DEV int &I(int w) const { return i[w * stride]; }
 };
@@ -175,6 +189,66 @@ struct LaneGame {
 
     RGS_DEV LaneGame(const FastParams<T> &P_, const LaneTab<T> *tab_, const S &s_) : P(P_), tab(tab_), s(s_) {}
 
+    // Event times.  The fp32 throughput mode works in step-relative time (t_ = 0 at the start of every step).  The
+    // fp64 instantiation exists to validate this formulation against the oracle, so it keeps the reference's
+    // ABSOLUTE clock arithmetic (T[i] = t_ + dt_col_ i :201, t_col - t_ < dt_ :501, base_idx :237, dt_t :254):
+    // for contacts resting on a grid time the rounding of t_ decides between two columns.
+    static constexpr bool kAbsClock = sizeof(T) == 8;
+    mutable T t0 = T(0);
+    RGS_DEV T col_time(int c) const {
+        if constexpr (kAbsClock) return t0 + P.d.dt_col * T(c);
+        else return P.d.dt_col * T(c);
+    }
+    RGS_DEV T since_t0(T t) const {
+        if constexpr (kAbsClock) return t - t0;
+        else return t;
+    }
+    RGS_DEV bool in_step(T t) const { return since_t0(t) < P.d.dt; }
+
+    // cumulative correctOverlap offset of body e at column c > CS[e]
+    RGS_DEV void off_at(int e, int c, T &ox, T &oy) const {
+        if (c >= s.I(S::FL + e)) { ox = s.F(S::OFF + 2 * e); oy = s.F(S::OFF + 2 * e + 1); }
+        else if (c < s.I(S::FF + e)) { ox = T(0); oy = T(0); }
+        else { ox = s.TR(e, c, 0); oy = s.TR(e, c, 1); }
+    }
+    RGS_DEV T off_at1(int e, int a, int c) const {
+        if (c >= s.I(S::FL + e)) return s.F(S::OFF + 2 * e + a);
+        if (c < s.I(S::FF + e)) return T(0);
+        return s.TR(e, c, a);
+    }
+    static RGS_DEV int word_bits(float x) { int b; memcpy(&b, &x, 4); return b; }
+    static RGS_DEV int word_bits(double x) { long long b; memcpy(&b, &x, 8); return (int)(b ^ (b >> 32)); }
+    // correctOverlap moved body e by (fx, fy) at column c > FL[e]: the offset in force so far stays the offset of
+    // the columns FL[e] .. c-1 (written to the track unless this is the segment's first fix)
+    RGS_DEV void record_fix(int e, int c, T fx, T fy) const {
+        const int fl = s.I(S::FL + e);
+        const T ox = s.F(S::OFF + 2 * e), oy = s.F(S::OFF + 2 * e + 1);
+        if (fl == s.I(S::CS + e)) {
+            s.I(S::FF + e) = c;
+        } else {
+            int ts = s.I(S::TS + e);
+#pragma unroll 1
+            for (int k = fl; k < c; ++k) {
+                s.TR(e, k, 0) = ox; s.TR(e, k, 1) = oy;
+                ts = ts * 31 + (word_bits(ox) ^ (word_bits(oy) * 7) ^ k);
+            }
+            s.I(S::TS + e) = ts;
+        }
+        s.F(S::OFF + 2 * e) = ox + fx; s.F(S::OFF + 2 * e + 1) = oy + fy;
+        s.I(S::FL + e) = c;
+    }
+
+    // event record of the launch: counters in the scratch record, flushed to the game's int64 record at the end
+    RGS_DEV void ev_add(int k, int n = 1) const { s.I(S::EVC + k) += n; }
+    RGS_DEV void hash_ev(long long live, int kind, int i, int j, int goal) const {
+        unsigned long long h = ((unsigned long long)(unsigned)s.I(S::EVC + 16) << 32) | (unsigned)s.I(S::EVC + RGS_EV_HASH);
+        h ^= ((unsigned long long)live << 16) | ((unsigned long long)kind << 12) | ((unsigned long long)i << 8) |
+             ((unsigned long long)(j < 0 ? 15 : j) << 4) | (unsigned long long)goal;   // == hash_event() of rgs_device.cuh
+        h *= 0x100000001B3ULL;
+        s.I(S::EVC + RGS_EV_HASH) = (int)(unsigned)h;
+        s.I(S::EVC + 16) = (int)(unsigned)(h >> 32);
+    }
+
     // state of body e at column c >= CS[e]-1 (position includes the correctOverlap offsets)
     RGS_DEV void eval(int e, int c, T &px, T &py, T &vx, T &vy) const {
         const int j = c - s.I(S::CS + e);
@@ -189,9 +263,10 @@ struct LaneGame {
         const LaneGK<T> gk = tab->e[ty][j];
         const T g = gk.g, k = gk.k, tj = P.d.dt_col * T(j);
         const T wx = svx - ux, wy = svy - uy;
-        const int late = (c >= s.I(S::FL + e)) ? 0 : 2;
-        px = fm(wx, k, fm(ux, tj, spx)) + s.F(S::OFF + 4 * e + late);
-        py = fm(wy, k, fm(uy, tj, spy)) + s.F(S::OFF + 4 * e + late + 1);
+        T ox, oy;
+        off_at(e, c, ox, oy);
+        px = fm(wx, k, fm(ux, tj, spx)) + ox;
+        py = fm(wy, k, fm(uy, tj, spy)) + oy;
         vx = fm(wx, g, ux);
         vy = fm(wy, g, uy);
     }
@@ -200,9 +275,11 @@ struct LaneGame {
     RGS_DEV void start_segment(int e, int c, T px, T py, T vx, T vy, T qx, T qy, T qvx, T qvy) const {
         s.F(S::PRV + 4 * e) = qx; s.F(S::PRV + 4 * e + 1) = qy; s.F(S::PRV + 4 * e + 2) = qvx; s.F(S::PRV + 4 * e + 3) = qvy;
         s.F(S::SP + 4 * e) = px; s.F(S::SP + 4 * e + 1) = py; s.F(S::SP + 4 * e + 2) = vx; s.F(S::SP + 4 * e + 3) = vy;
-        s.F(S::OFF + 4 * e) = T(0); s.F(S::OFF + 4 * e + 1) = T(0); s.F(S::OFF + 4 * e + 2) = T(0); s.F(S::OFF + 4 * e + 3) = T(0);
+        s.F(S::OFF + 2 * e) = T(0); s.F(S::OFF + 2 * e + 1) = T(0);
         s.I(S::CS + e) = c;
         s.I(S::FL + e) = c;
+        s.I(S::FF + e) = c;
+        s.I(S::TS + e) = 0;
     }
 
     // bounding interval of body e over columns CS[e]..50 (monotone-velocity bound + offsets)
@@ -211,13 +288,20 @@ struct LaneGame {
         const int cs = s.I(S::CS + e);
         const int rem = kGrid - cs;
         const T trem = P.d.dt_col * T(rem), gE = tab->e[ty][rem].g;
+        const int ff = s.I(S::FF + e), fl = s.I(S::FL + e);
 #pragma unroll
         for (int a = 0; a < 2; ++a) {
             const T p = s.F(S::SP + 4 * e + a), v = s.F(S::SP + 4 * e + 2 + a), u = s.F(S::CMD + 2 * e + a);
             const T vE = fm(v - u, gE, u);
-            const T o1 = s.F(S::OFF + 4 * e + a), o2 = s.F(S::OFF + 4 * e + 2 + a);
-            const T lo = p + tmin(T(0), tmin(v, vE) * trem) + tmin(T(0), tmin(o1, o2));
-            const T hi = p + tmax(T(0), tmax(v, vE) * trem) + tmax(T(0), tmax(o1, o2));
+            const T o1 = s.F(S::OFF + 2 * e + a);
+            T olo = tmin(T(0), o1), ohi = tmax(T(0), o1);
+#pragma unroll 1
+            for (int k = ff; k < fl; ++k) {   // a segment fixed more than once: hull of its cumulative offsets
+                const T o = s.TR(e, k, a);
+                olo = tmin(olo, o); ohi = tmax(ohi, o);
+            }
+            const T lo = p + tmin(T(0), tmin(v, vE) * trem) + olo;
+            const T hi = p + tmax(T(0), tmax(v, vE) * trem) + ohi;
             s.F(S::BB + 4 * e + 2 * a) = lo;
             s.F(S::BB + 4 * e + 2 * a + 1) = hi;
         }
@@ -270,8 +354,8 @@ struct LaneGame {
     // ---- narrow phase: one item searched over the columns (insertCollisions :362-507, one test) ----
     // mirrored single-axis view of body a for wall wk: q = sgn * coordinate, overlap <=> q >= lim
     struct Axis {
-        T sp, sv, u, w0, off_t, off_b;
-        int cs, fl, ty;
+        T sp, sv, u, w0, off_t, sgn;
+        int cs, fl, ff, ty, e, ax;
     };
     RGS_DEV Axis axis_of(int a, int wk) const {
         Axis A;
@@ -280,19 +364,23 @@ struct LaneGame {
         A.ty = (a == PK);
         A.cs = s.I(S::CS + a);
         A.fl = s.I(S::FL + a);
+        A.ff = s.I(S::FF + a);
+        A.e = a; A.ax = ax; A.sgn = sgn;
         A.sp = sgn * s.F(S::SP + 4 * a + ax);
         A.sv = sgn * s.F(S::SP + 4 * a + 2 + ax);
         A.u = sgn * s.F(S::CMD + 2 * a + ax);
         A.w0 = A.sv - A.u;
-        A.off_t = sgn * s.F(S::OFF + 4 * a + ax);
-        A.off_b = sgn * s.F(S::OFF + 4 * a + 2 + ax);
+        A.off_t = sgn * s.F(S::OFF + 2 * a + ax);
         return A;
     }
     // q and its velocity at column c >= cs (closed form from the segment start)
+    RGS_DEV T axis_off(const Axis &A, int c) const {   // mirrored cumulative offset at column c
+        return c >= A.fl ? A.off_t : (c < A.ff ? T(0) : A.sgn * s.TR(A.e, c, A.ax));
+    }
     RGS_DEV void axis_at(const Axis &A, int c, T &q, T &v) const {
         const int j = c - A.cs;
         const LaneGK<T> gk = tab->e[A.ty][j];
-        q = fm(A.w0, gk.k, fm(A.u, P.d.dt_col * T(j), A.sp)) + (c >= A.fl ? A.off_t : A.off_b);
+        q = fm(A.w0, gk.k, fm(A.u, P.d.dt_col * T(j), A.sp)) + axis_off(A, c);
         v = fm(A.w0, gk.g, A.u);
         if (j == 0) { q = A.sp; v = A.sv; }
     }
@@ -338,14 +426,13 @@ struct LaneGame {
         axis_at(A, c0, p, w);
         w = w - A.u;
         const T R = tab->e[A.ty][1].g, k1 = tab->e[A.ty][1].k, uh = A.u * P.d.dt_col;
-        const T doff = A.off_t - A.off_b;
         bool was_over = false;
 #pragma unroll 1
         for (int c = c0; c <= kGrid; ++c) {
             const bool over = p >= lim;
             if (over && vm > T(0)) {
-                const T tc = P.d.dt_col * T(c - 1) + tmax(T(0), (lim - pm) / vm);
-                if (tc < P.d.dt) { t_out = tc; return c; }
+                const T tc = col_time(c - 1) + tmax(T(0), (lim - pm) / vm);
+                if (in_step(tc)) { t_out = tc; return c; }
             }
             // left the wall again on a concave arc with no pending jump: it cannot come back
             if (was_over && !over && A.fl <= c && w > T(0)) break;
@@ -355,7 +442,7 @@ struct LaneGame {
             vm = A.u + w;
             p = fm(w, k1, p + uh);
             w = w * R;
-            if (c + 1 == A.fl) p += doff;
+            if (c + 1 <= A.fl && c + 1 >= A.ff) p += axis_off(A, c + 1) - axis_off(A, c);
         }
         return kGrid + 1;
     }
@@ -363,8 +450,8 @@ struct LaneGame {
     // register copy of what the position of a body at a column depends on (the column loops of
     // search_pair / march_pair evaluate positions only; same arithmetic as eval())
     struct PosSeg {
-        T spx, spy, wx, wy, ux, uy, otx, oty, obx, oby;
-        int cs, fl, ty, e;
+        T spx, spy, wx, wy, ux, uy, otx, oty;
+        int cs, fl, ff, ty, e;
     };
     RGS_DEV PosSeg pos_seg(int e) const {
         PosSeg g;
@@ -372,11 +459,11 @@ struct LaneGame {
         g.ty = (e == PK);
         g.cs = s.I(S::CS + e);
         g.fl = s.I(S::FL + e);
+        g.ff = s.I(S::FF + e);
         g.spx = s.F(S::SP + 4 * e); g.spy = s.F(S::SP + 4 * e + 1);
         g.ux = s.F(S::CMD + 2 * e); g.uy = s.F(S::CMD + 2 * e + 1);
         g.wx = s.F(S::SP + 4 * e + 2) - g.ux; g.wy = s.F(S::SP + 4 * e + 3) - g.uy;
-        g.otx = s.F(S::OFF + 4 * e); g.oty = s.F(S::OFF + 4 * e + 1);
-        g.obx = s.F(S::OFF + 4 * e + 2); g.oby = s.F(S::OFF + 4 * e + 3);
+        g.otx = s.F(S::OFF + 2 * e); g.oty = s.F(S::OFF + 2 * e + 1);
         return g;
     }
     RGS_DEV void pos_at(const PosSeg &g, int c, T &px, T &py) const {
@@ -388,9 +475,13 @@ struct LaneGame {
         }
         const LaneGK<T> gk = tab->e[g.ty][j];
         const T tj = P.d.dt_col * T(j);
-        const bool late = c >= g.fl;
-        px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + (late ? g.otx : g.obx);
-        py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + (late ? g.oty : g.oby);
+        T ox = g.otx, oy = g.oty;
+        if (c < g.fl) {
+            if (c < g.ff) { ox = T(0); oy = T(0); }
+            else { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
+        }
+        px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + ox;
+        py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + oy;
     }
 
     // position and velocity at column c (velocity: same arithmetic as eval())
@@ -403,9 +494,13 @@ struct LaneGame {
         }
         const LaneGK<T> gk = tab->e[g.ty][j];
         const T tj = P.d.dt_col * T(j);
-        const bool late = c >= g.fl;
-        px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + (late ? g.otx : g.obx);
-        py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + (late ? g.oty : g.oby);
+        T ox = g.otx, oy = g.oty;
+        if (c < g.fl) {
+            if (c < g.ff) { ox = T(0); oy = T(0); }
+            else { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
+        }
+        px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + ox;
+        py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + oy;
         vx = fm(g.wx, gk.g, g.ux);
         vy = fm(g.wy, gk.g, g.uy);
     }
@@ -450,8 +545,8 @@ struct LaneGame {
         const int tya = (a == PK), tyb = (b == PK);
         const T thr = P.d.ov_le[tya][tyb], sigma = P.d.sig[tya][tyb];
         const T h = P.d.dt_col;
-        // no skipping while a correctOverlap jump of either body is still ahead
-        const bool jump = s.I(S::FL + a) > base || s.I(S::FL + b) > base;
+        // no skipping while a correctOverlap offset change of either body is still ahead
+        const int fl_ab = s.I(S::FL + a) > s.I(S::FL + b) ? s.I(S::FL + a) : s.I(S::FL + b);
         const T eps = drift_bound(a, b), inv_h = T(1) / h;
         int c = base;
         const PosSeg ga = pos_seg(a), gb = pos_seg(b);
@@ -469,12 +564,12 @@ struct LaneGame {
                 const T dpdv = fm(dpx, dvx, dpy * dvy), dvdv = fm(dvx, dvx, dvy * dvy), dpdp = fm(dpx, dpx, dpy * dpy);
                 const T d = dpdv * dpdv - dvdv * (dpdp - sigma * sigma);
                 if (dpdv < T(0) && d >= T(0)) {
-                    const T tc = h * T(c - 1) + tmax(T(0), -(dpdv + T(sqrt(d))) / dvdv);
-                    if (tc < P.d.dt) { t_out = tc; return c; }
+                    const T tc = col_time(c - 1) + tmax(T(0), -(dpdv + T(sqrt(d))) / dvdv);
+                    if (in_step(tc)) { t_out = tc; return c; }
                 }
                 ++c;
             } else {
-                c += 1 + (jump ? 0 : free_columns(-ex, -ey, bvx - avx, bvy - avy, ssq, sigma, eps, inv_h));
+                c += 1 + (c < fl_ab ? 0 : free_columns(-ex, -ey, bvx - avx, bvy - avy, ssq, sigma, eps, inv_h));
             }
         }
         return kGrid + 1;
@@ -562,7 +657,7 @@ struct LaneGame {
     // correctOverlap on the columns after an impact (:285-297): visit the columns of the pair's new
     // segments where it can still overlap (conservative advancement on the relative speed bound,
     // as in search_pair), record the position offsets
-    RGS_DEV void march_pair(int bi, int bj, int base, long long *ev) const {
+    RGS_DEV void march_pair(int bi, int bj, int base) const {
         const int tyi = (bi == PK), tyj = (bj == PK);
         const T thr = P.d.ov_lt[tyi][tyj], sigma = P.d.sig[tyi][tyj];
         const T eps = drift_bound(bi, bj), inv_h = T(1) / P.d.dt_col;
@@ -579,17 +674,11 @@ struct LaneGame {
                 const T overlap = sigma - T(sqrt(ssq));
                 const T si = P.d.fix_coef[tyi][tyj] * overlap, sj = P.d.fix_coef[tyj][tyi] * overlap;
                 const T fax = -(si * dx), fay = -(si * dy), fbx = sj * dx, fby = sj * dy;
-                // the offsets in force before this column stay valid for the columns before it
-                const bool fresh_i = s.I(S::FL + bi) < c, fresh_j = s.I(S::FL + bj) < c;
-                if (fresh_i) { s.F(S::OFF + 4 * bi + 2) = s.F(S::OFF + 4 * bi); s.F(S::OFF + 4 * bi + 3) = s.F(S::OFF + 4 * bi + 1); }
-                if (fresh_j) { s.F(S::OFF + 4 * bj + 2) = s.F(S::OFF + 4 * bj); s.F(S::OFF + 4 * bj + 3) = s.F(S::OFF + 4 * bj + 1); }
-                s.F(S::OFF + 4 * bi) += fax; s.F(S::OFF + 4 * bi + 1) += fay;
-                s.F(S::OFF + 4 * bj) += fbx; s.F(S::OFF + 4 * bj + 1) += fby;
-                s.I(S::FL + bi) = c;
-                s.I(S::FL + bj) = c;
+                record_fix(bi, c, fax, fay);
+                record_fix(bj, c, fbx, fby);
                 gi = pos_seg(bi);
                 gj = pos_seg(bj);
-                ev[RGS_EV_OVERLAP_FIXES]++;
+                ev_add(RGS_EV_OVERLAP_FIXES);
                 ++c;
             } else {
                 c += 1 + free_columns(dx, dy, bvx - avx, bvy - avy, ssq, sigma, eps, inv_h);
@@ -598,7 +687,7 @@ struct LaneGame {
     }
     // same for a body and the wall it hit (:329-340).  q(c) is convex or concave on the new
     // segment and starts inside the limit, so it can only overlap again if its last column does.
-    RGS_DEV void march_wall(int bi, int wk, int base, long long *ev) const {
+    RGS_DEV void march_wall(int bi, int wk, int base) const {
         const Axis A = axis_of(bi, wk);
         const int ax = wk >= 2 ? 0 : 1;
         const T sgn = (wk == WALL_UP || wk == WALL_RIGHT) ? T(1) : T(-1);
@@ -619,11 +708,8 @@ struct LaneGame {
                 const T pc = tmin(p - P.d.wall_fix * (p - lim), lim_in);
                 const T f = pc - p;
                 p = pc;
-                s.F(S::OFF + 4 * bi + 2 + ax) = s.F(S::OFF + 4 * bi + ax);
-                s.F(S::OFF + 4 * bi + 2 + (1 - ax)) = s.F(S::OFF + 4 * bi + (1 - ax));
-                s.F(S::OFF + 4 * bi + ax) += sgn * f;
-                s.I(S::FL + bi) = c;
-                ev[RGS_EV_OVERLAP_FIXES]++;
+                record_fix(bi, c, ax == 0 ? sgn * f : T(0), ax == 0 ? T(0) : sgn * f);
+                ev_add(RGS_EV_OVERLAP_FIXES);
             }
         }
     }
@@ -631,16 +717,16 @@ struct LaneGame {
     // ---- execute one popped event (carryOutFirstCollision :237-345): advance the bodies to the time of
     // impact, resolve, start their new segments at column `base`, correctOverlap on the later columns.
     // Returns the second body to re-scan (-1 for a wall event); goal = 1 (team A) / 2 (team B) / 0.
-    RGS_DEV_BIG int resolve(int ei, int ej, int ekind, T et, int &base, int &goal, long long *ev, double *dmg, long long live,
+    RGS_DEV_BIG int resolve(int ei, int ej, int ekind, T et, int &base, int &goal, double *dmg, long long live,
                             double *dv_sq_out = nullptr) const {
         int rj = -1;
         goal = 0;
         {
-            int nb = (int)floor(et / P.d.dt_col) + 1;  // :237
-            if (nb > kGrid) { nb = kGrid; ev[RGS_EV_BASE_CLAMP]++; }
+            int nb = (int)floor(since_t0(et) / P.d.dt_col) + 1;  // :237
+            if (nb > kGrid) { nb = kGrid; ev_add(RGS_EV_BASE_CLAMP); }
             if (nb > base) base = nb;  // event times never run backwards by more than a rounding
         }
-        const T dt_t = et - P.d.dt_col * T(base - 1);  // :254 / :308
+        const T dt_t = et - col_time(base - 1);  // :254 / :308
         const T h_rest = P.d.dt_col - dt_t;
         const int tyi = (ei == PK);
         T qix, qiy, qvix, qviy;
@@ -676,9 +762,9 @@ struct LaneGame {
                     if (dv_sq_out) *dv_sq_out = dv_sq;
                     dmg[ei * NP + ej] += (double)P.d.mass[tyi] * dv_sq;
                     dmg[ej * NP + ei] += (double)P.d.mass[tyj] * dv_sq;
-                    ev[RGS_EV_PLAYER_PLAYER]++;
+                    ev_add(RGS_EV_PLAYER_PLAYER);
                 } else {
-                    ev[RGS_EV_PLAYER_PUCK]++;
+                    ev_add(RGS_EV_PLAYER_PUCK);
                 }
                 vix -= fi * dpx; viy -= fi * dpy;
                 vjx += fj * dpx; vjy += fj * dpy;
@@ -695,12 +781,12 @@ struct LaneGame {
                     const T si = P.d.fix_coef[tyi][tyj] * overlap, sj = P.d.fix_coef[tyj][tyi] * overlap;
                     pix -= si * dx; piy -= si * dy;
                     pjx += sj * dx; pjy += sj * dy;
-                    ev[RGS_EV_OVERLAP_FIXES]++;
+                    ev_add(RGS_EV_OVERLAP_FIXES);
                 }
             }
             start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
             start_segment(ej, base, pjx, pjy, vjx, vjy, qjx, qjy, qvjx, qvjy);
-            march_pair(ei, ej, base, ev);
+            march_pair(ei, ej, base);
             update_bbox(ej);
             rj = ej;
         } else {  // wall :300-343
@@ -714,7 +800,7 @@ struct LaneGame {
                                  piy > -P.d.half_goal;  // :321-322
             if (is_goal) {
                 goal = ekind == WALL_RIGHT ? 1 : 2;
-                ev[goal == 1 ? RGS_EV_GOALS_A : RGS_EV_GOALS_B]++;
+                ev_add(goal == 1 ? RGS_EV_GOALS_A : RGS_EV_GOALS_B);
                 pix = piy = vix = viy = T(0);  // puck reset :325
             } else {
                 advance_axis(pix, vix, uix, h_rest, P.neg_inv_tau[tyi]);
@@ -727,16 +813,16 @@ struct LaneGame {
                     if (q >= lim) {
                         const T qc = sgn * tmin(q - P.d.wall_fix * (q - lim), lim_in);
                         if (xa) pix = qc; else piy = qc;
-                        ev[RGS_EV_OVERLAP_FIXES]++;
+                        ev_add(RGS_EV_OVERLAP_FIXES);
                     }
                 }
             }
-            ev[RGS_EV_WALL_UP + ekind]++;
+            ev_add(RGS_EV_WALL_UP + ekind);
             start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
-            if (!is_goal) march_wall(ei, ekind, base, ev);
+            if (!is_goal) march_wall(ei, ekind, base);
         }
         update_bbox(ei);
-        hash_event(ev, live, ekind, ei, ej, goal);
+        hash_ev(live, ekind, ei, ej, goal);
         return rj;
     }
 
@@ -748,17 +834,19 @@ struct LaneGame {
     // executed: their side effects (event counters, the order-sensitive event hash, damage, push sequence
     // numbers) are replayed exactly and the loop resumes for the last partial period.  Identical results,
     // ~10 % fewer instructions overall (those steps were 12 % of them).
+    // The snapshot's run-time-indexed words live in the lane's global scratch area behind the tracks (JF / JI),
+    // not in local memory; only its scalars are registers.
     static constexpr bool kJamFF = NT <= 3;
-    static constexpr int kJamLog = 6;
     struct JamSnap {
-        T f[S::QT + E];                 // SP, CMD, PRV, OFF, BB, and QT of the queued owners
-        int i[3 * E];                   // CS, FL, QI & 0xFFFF of the queued owners
         unsigned qmask, owners, wbits, pbits, ranks;
-        int base, ri, rj, scored, seq, counter;
-        long long ev[RGS_N_EVENTS];
-        int log_n, log_ev[kJamLog];     // kind | i << 4 | (j + 1) << 8 | goal << 12 per executed / discarded event
-        double log_dv[kJamLog];         // dv_sq of a player-player impact, else -1
+        int base, ri, rj, scored, seq, counter, log_n;
     };
+    // JF: SP, CMD, PRV, OFF, BB, and QT of the queued owners.  JI: CS, FL, QI & 0xFFFF, FF, TS [5E]; the event
+    // counters [17]; per logged event kind | i << 4 | (j + 1) << 8 | goal << 12 [kJamLog] and the two halves of
+    // dv_sq of a player-player impact (-1: none) [2 kJamLog]
+    static constexpr int JI_EV = 5 * E, JI_LOG = 5 * E + 17, JI_DV = JI_LOG + kJamLog;
+    RGS_DEV T &JF(int w) const { return s.trk[(size_t)(S::TRK_WORDS + w) * s.tstride]; }
+    RGS_DEV int &JI(int w) const { return *reinterpret_cast<int *>(&s.trk[(size_t)(S::TRK_WORDS + S::JAM_F + w) * s.tstride]); }
     static RGS_DEV bool same_bits(T a, T b) {
         if constexpr (sizeof(T) == 4) {
             unsigned x, y;
@@ -785,20 +873,22 @@ struct LaneGame {
         return r;
     }
     RGS_DEV void jam_snapshot(JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
-                              bool scored, int seq, int counter, const long long *ev) const {
+                              bool scored, int seq, int counter) const {
 #pragma unroll 1
-        for (int w = 0; w < S::QT; ++w) J.f[w] = s.F(w);
+        for (int w = 0; w < S::QT; ++w) JF(w) = s.F(w);
 #pragma unroll 1
         for (int e = 0; e < E; ++e) {
-            J.f[S::QT + e] = s.F(S::QT + e);
-            J.i[e] = s.I(S::CS + e);
-            J.i[E + e] = s.I(S::FL + e);
-            J.i[2 * E + e] = s.I(S::QI + e) & 0xFFFF;
+            JF(S::QT + e) = s.F(S::QT + e);
+            JI(e) = s.I(S::CS + e);
+            JI(E + e) = s.I(S::FL + e);
+            JI(2 * E + e) = s.I(S::QI + e) & 0xFFFF;
+            JI(3 * E + e) = s.I(S::FF + e);
+            JI(4 * E + e) = s.I(S::TS + e);
         }
+#pragma unroll 1
+        for (int k = 0; k < 17; ++k) JI(JI_EV + k) = s.I(S::EVC + k);
         J.qmask = qmask; J.owners = owners; J.wbits = wbits; J.pbits = pbits; J.ranks = queue_ranks(qmask);
         J.base = base; J.ri = ri; J.rj = rj; J.scored = scored; J.seq = seq; J.counter = counter;
-#pragma unroll 1
-        for (int k = 0; k < RGS_N_EVENTS; ++k) J.ev[k] = ev[k];
         J.log_n = 0;
     }
     RGS_DEV bool jam_same(const JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
@@ -808,17 +898,19 @@ struct LaneGame {
             return false;
 #pragma unroll 1
         for (int w = 0; w < S::QT; ++w)
-            if (!same_bits(J.f[w], s.F(w))) return false;
+            if (!same_bits(JF(w), s.F(w))) return false;
 #pragma unroll 1
         for (int e = 0; e < E; ++e) {
-            if (J.i[e] != s.I(S::CS + e) || J.i[E + e] != s.I(S::FL + e)) return false;
+            if (JI(e) != s.I(S::CS + e) || JI(E + e) != s.I(S::FL + e) || JI(3 * E + e) != s.I(S::FF + e) ||
+                JI(4 * E + e) != s.I(S::TS + e))
+                return false;
             if ((qmask >> e) & 1u)
-                if (!same_bits(J.f[S::QT + e], s.F(S::QT + e)) || J.i[2 * E + e] != (s.I(S::QI + e) & 0xFFFF)) return false;
+                if (!same_bits(JF(S::QT + e), s.F(S::QT + e)) || JI(2 * E + e) != (s.I(S::QI + e) & 0xFFFF)) return false;
         }
         return J.ranks == queue_ranks(qmask);
     }
     // skip the whole periods that fit before the loop bound; returns the new counter
-    RGS_DEV int jam_fast_forward(const JamSnap &J, int counter, int &seq, unsigned qmask, long long *ev, double *dmg, long long live) const {
+    RGS_DEV int jam_fast_forward(const JamSnap &J, int counter, int &seq, unsigned qmask, double *dmg, long long live) const {
         const int period = counter - J.counter;
         const int m = (kCounterLim - counter) / period;
         if (m <= 0 || J.log_n != period) return counter;
@@ -827,17 +919,21 @@ struct LaneGame {
                                        RGS_EV_WALL_LEFT, RGS_EV_PLAYER_PLAYER, RGS_EV_PLAYER_PUCK, RGS_EV_DISCARDED,
                                        RGS_EV_BASE_CLAMP, RGS_EV_OVERLAP_FIXES};
 #pragma unroll 1
-        for (int k = 0; k < (int)(sizeof(kAdd) / sizeof(int)); ++k) ev[kAdd[k]] += (long long)m * (ev[kAdd[k]] - J.ev[kAdd[k]]);
+        for (int k = 0; k < (int)(sizeof(kAdd) / sizeof(int)); ++k)
+            s.I(S::EVC + kAdd[k]) += m * (s.I(S::EVC + kAdd[k]) - JI(JI_EV + kAdd[k]));
 #pragma unroll 1
         for (int r = 0; r < m; ++r)
 #pragma unroll 1
             for (int l = 0; l < period; ++l) {
-                const int c = J.log_ev[l];
+                const int c = JI(JI_LOG + l);
                 const int kind = c & 15, i = (c >> 4) & 15, j = ((c >> 8) & 15) - 1, goal = (c >> 12) & 3;
-                hash_event(ev, live, kind, i, j, goal);
-                if (J.log_dv[l] >= 0.0) {  // damage :277-282, same operands in the same order
-                    dmg[i * NP + j] += (double)P.d.mass[i == PK] * J.log_dv[l];
-                    dmg[j * NP + i] += (double)P.d.mass[j == PK] * J.log_dv[l];
+                hash_ev(live, kind, i, j, goal);
+                const unsigned long long db = ((unsigned long long)(unsigned)JI(JI_DV + 2 * l + 1) << 32) | (unsigned)JI(JI_DV + 2 * l);
+                double dv;
+                memcpy(&dv, &db, 8);
+                if (dv >= 0.0) {  // damage :277-282, same operands in the same order
+                    dmg[i * NP + j] += (double)P.d.mass[i == PK] * dv;
+                    dmg[j * NP + i] += (double)P.d.mass[j == PK] * dv;
                 }
             }
         // the sequence numbers of the queued events advance by whole periods too (their order is what matters)
@@ -852,15 +948,18 @@ struct LaneGame {
     }
     RGS_DEV void jam_log(JamSnap &J, int kind, int i, int j, int goal, double dv_sq) const {
         if (J.log_n < kJamLog) {
-            J.log_ev[J.log_n] = kind | (i << 4) | ((j + 1) << 8) | (goal << 12);
-            J.log_dv[J.log_n] = dv_sq;
+            JI(JI_LOG + J.log_n) = kind | (i << 4) | ((j + 1) << 8) | (goal << 12);
+            unsigned long long db;
+            memcpy(&db, &dv_sq, 8);
+            JI(JI_DV + 2 * J.log_n) = (int)(unsigned)db;
+            JI(JI_DV + 2 * J.log_n + 1) = (int)(unsigned)(db >> 32);
         }
         J.log_n++;
     }
 
     // ---- the event loop of one game-step (GameSim::updateSim :136-150) on the flagged items ----
     // returns the loop counter of the step
-    RGS_DEV int event_loop(Bits<4 * E> &wb, Bits<NPAIR> &pb, double &sa, double &sb, long long *ev, double *dmg, long long live) const {
+    RGS_DEV int event_loop(Bits<4 * E> &wb, Bits<NPAIR> &pb, double &sa, double &sb, double *dmg, long long live) const {
         int counter = 1;
         if (wb.any() || pb.any()) {
             unsigned qmask = 0, fmask = 0, owners = (1u << E) - 1u;
@@ -873,10 +972,10 @@ struct LaneGame {
                 if constexpr (kJamFF) {
                     if (counter >= 8) {
                         if ((counter & 7) == 0) {
-                            jam_snapshot(J, qmask, owners, wb.w[0], pb.w[0], base, ri, rj, scored, seq, counter, ev);
+                            jam_snapshot(J, qmask, owners, wb.w[0], pb.w[0], base, ri, rj, scored, seq, counter);
                         } else if (J.counter != 0 && counter - J.counter <= kJamLog &&
                                    jam_same(J, qmask, owners, wb.w[0], pb.w[0], base, ri, rj, scored)) {
-                            counter = jam_fast_forward(J, counter, seq, qmask, ev, dmg, live);
+                            counter = jam_fast_forward(J, counter, seq, qmask, dmg, live);
                             J.counter = 0;
                         }
                     }
@@ -896,8 +995,8 @@ struct LaneGame {
                 pop(qmask, ei, ej, ekind, et);
                 ri = ei; rj = -1; owners = 0;  // nothing to re-scan unless the event executes
                 if ((ei == PK || ej == PK) && scored) {  // :230-231
-                    ev[RGS_EV_DISCARDED]++;
-                    hash_event(ev, live, DISCARD, ei, ej, 0);
+                    ev_add(RGS_EV_DISCARDED);
+                    hash_ev(live, DISCARD, ei, ej, 0);
                     if constexpr (kJamFF)
                         if (J.counter != 0) jam_log(J, DISCARD, ei, ej, 0, -1.0);
                     ++counter;
@@ -905,7 +1004,7 @@ struct LaneGame {
                 }
                 int goal = 0;
                 double dv_sq = -1.0;
-                rj = resolve(ei, ej, ekind, et, base, goal, ev, dmg, live, &dv_sq);
+                rj = resolve(ei, ej, ekind, et, base, goal, dmg, live, &dv_sq);
                 if constexpr (kJamFF)
                     if (J.counter != 0) jam_log(J, ekind, ei, ej, goal, dv_sq);
                 if (goal) {
@@ -924,97 +1023,19 @@ struct LaneGame {
                 if (rj >= 0) reflag_pairs(rj, ei, pb);
                 ++counter;
             }
-            if (qmask != 0) ev[RGS_EV_COUNTER_LIMIT]++;
+            if (qmask != 0) ev_add(RGS_EV_COUNTER_LIMIT);
         }
         return counter;
     }
 
-    // ---- event_loop cut at its iteration boundary (rollout_lane_warp below): the loop-carried variables live in
-    // EvState so that a lane can stop after any iteration and continue later, when enough lanes of its warp are
-    // in the loop too.  event_begin + event_iter until it returns true == event_loop, statement for statement.
-    struct EvState {
-        Bits<4 * E> wb;
-        Bits<NPAIR> pb;
-        unsigned qmask, owners;
-        int seq, base, ri, rj, counter;
-        bool scored;
-    };
-    // (the jam snapshot J is passed separately: its run-time-indexed arrays live in local memory, and a struct that
-    // held both would drag the scalars above there too)
-    RGS_DEV void event_begin(EvState &X, JamSnap &J) const {
-        X.qmask = 0; X.owners = (1u << E) - 1u;
-        X.seq = 0; X.base = 1; X.ri = -1; X.rj = -1; X.counter = 1;
-        X.scored = false;
-        J.counter = 0;
-    }
-    // returns true when the step has no more events to process (X.counter = the loop counter of the step)
-    RGS_DEV bool event_iter(EvState &X, JamSnap &J, double &sa, double &sb, long long *ev, double *dmg, long long live) const {
-        if constexpr (kJamFF) {
-            if (X.counter >= 8) {
-                if ((X.counter & 7) == 0) {
-                    jam_snapshot(J, X.qmask, X.owners, X.wb.w[0], X.pb.w[0], X.base, X.ri, X.rj, X.scored, X.seq, X.counter, ev);
-                } else if (J.counter != 0 && X.counter - J.counter <= kJamLog &&
-                           jam_same(J, X.qmask, X.owners, X.wb.w[0], X.pb.w[0], X.base, X.ri, X.rj, X.scored)) {
-                    X.counter = jam_fast_forward(J, X.counter, X.seq, X.qmask, ev, dmg, live);
-                    J.counter = 0;
-                }
-            }
-        }
-        unsigned fmask = 0;
-        run_items(X.wb, X.pb, X.owners, X.base, fmask);
-        if (X.ri < 0) {
-#pragma unroll 1
-            for (unsigned m = fmask; m != 0u; m &= m - 1u) push(low_bit(m), X.qmask, X.seq);  // ascending owners
-        } else {
-            if ((fmask >> X.ri) & 1u) push(X.ri, X.qmask, X.seq);
-            if (X.rj >= 0 && ((fmask >> X.rj) & 1u)) push(X.rj, X.qmask, X.seq);
-        }
-        if (X.qmask == 0 || X.counter >= kCounterLim) {
-            if (X.qmask != 0) ev[RGS_EV_COUNTER_LIMIT]++;
-            return true;
-        }
-        int ei, ej, ekind;
-        T et;
-        pop(X.qmask, ei, ej, ekind, et);
-        X.ri = ei; X.rj = -1; X.owners = 0;
-        if ((ei == PK || ej == PK) && X.scored) {
-            ev[RGS_EV_DISCARDED]++;
-            hash_event(ev, live, DISCARD, ei, ej, 0);
-            if constexpr (kJamFF)
-                if (J.counter != 0) jam_log(J, DISCARD, ei, ej, 0, -1.0);
-            ++X.counter;
-            return false;
-        }
-        int goal = 0;
-        double dv_sq = -1.0;
-        X.rj = resolve(ei, ej, ekind, et, X.base, goal, ev, dmg, live, &dv_sq);
-        if constexpr (kJamFF)
-            if (J.counter != 0) jam_log(J, ekind, ei, ej, goal, dv_sq);
-        if (goal) {
-            if (goal == 1) sa += 1.0; else sb += 1.0;
-            X.scored = true;
-        }
-        prune(X.qmask, ei, ej);
-        X.owners = 1u << ei;
-        flag_walls(ei, X.wb);
-        if (X.rj >= 0) {
-            X.owners |= 1u << X.rj;
-            flag_walls(X.rj, X.wb);
-        }
-        reflag_pairs(ei, -1, X.pb);
-        if (X.rj >= 0) reflag_pairs(X.rj, ei, X.pb);
-        ++X.counter;
-        return false;
-    }
-
-    // ---- one game-step with the state held in shared memory (SP/CMD hold the state and the commands;
-    // teams of more than 3, where the register form below would spill) ----
+    // ---- one game-step; SP / CMD of the scratch record hold the state and the commands between steps ----
     // returns the event-loop counter of the step (1 when nothing happened)
-    RGS_DEV int step(double &sa, double &sb, long long *ev, double *dmg, long long live) const {
+    RGS_DEV int step(double t_clock, double &sa, double &sb, double *dmg, long long live) const {
+        if constexpr (kAbsClock) t0 = (T)t_clock;
         Bits<4 * E> wb;
         Bits<NPAIR> pb;
         step_head(wb, pb);
-        const int counter = event_loop(wb, pb, sa, sb, ev, dmg, live);
+        const int counter = event_loop(wb, pb, sa, sb, dmg, live);
         step_commit();
         return counter;
     }
@@ -1030,11 +1051,12 @@ struct LaneGame {
                 const int ty = (e == PK);
                 s.I(S::CS + e) = 0;
                 s.I(S::FL + e) = 0;
+                s.I(S::FF + e) = 0;
+                s.I(S::TS + e) = 0;
                 T lohi[4];
 #pragma unroll
                 for (int a = 0; a < 2; ++a) {
-                    s.F(S::OFF + 4 * e + a) = T(0);
-                    s.F(S::OFF + 4 * e + 2 + a) = T(0);
+                    s.F(S::OFF + 2 * e + a) = T(0);
                     const T p = s.F(S::SP + 4 * e + a), v = s.F(S::SP + 4 * e + 2 + a), u = s.F(S::CMD + 2 * e + a);
                     const T vE = fm(v - u, gE[ty], u);
                     lohi[2 * a] = p + tmin(T(0), tmin(v, vE) * trem) + T(0);
@@ -1074,104 +1096,6 @@ struct LaneGame {
         }
     }
 
-    // ---- the same step with the state in REGISTERS (st[4e+c], cmd[2p+a]; compile-time indices only):
-    // a contact-free step (69 % of the S0 steps) never touches shared memory ----
-    // bounding intervals + broad-phase flags of the whole-step segments: update_bbox / flag_walls /
-    // flag_pair with cs = 0 and no offsets, same arithmetic
-    RGS_DEV void head_flags(const T *st, const T *cmd, T *bb, Bits<4 * E> &wb, Bits<NPAIR> &pb) const {
-        const T trem = P.d.dt_col * T(kGrid);
-        const T sl = Slack<T>::v;
-        wb.clear();
-        pb.clear();
-#pragma unroll
-        for (int e = 0; e < E; ++e) {
-            const int ty = (e == PK);
-            const T gE = tab->e[ty][kGrid].g;
-#pragma unroll
-            for (int a = 0; a < 2; ++a) {
-                const T p = st[4 * e + a], v = st[4 * e + 2 + a], u = e == PK ? T(0) : cmd[2 * (e == PK ? 0 : e) + a];
-                const T vE = fm(v - u, gE, u);
-                bb[4 * e + 2 * a] = p + tmin(T(0), tmin(v, vE) * trem) + T(0);
-                bb[4 * e + 2 * a + 1] = p + tmax(T(0), tmax(v, vE) * trem) + T(0);
-            }
-            const T lx = P.lim_x[ty] - sl, ly = P.lim_y[ty] - sl;
-            if (bb[4 * e + 3] >= ly) wb.set(4 * e + WALL_UP);
-            if (bb[4 * e + 2] <= -ly) wb.set(4 * e + WALL_DOWN);
-            if (bb[4 * e + 1] >= lx) wb.set(4 * e + WALL_RIGHT);
-            if (bb[4 * e + 0] <= -lx) wb.set(4 * e + WALL_LEFT);
-        }
-#pragma unroll
-        for (int a = 0; a < E - 1; ++a)
-#pragma unroll
-            for (int b = a + 1; b < E; ++b) {
-                const T gx = tmax(T(0), tmax(bb[4 * a] - bb[4 * b + 1], bb[4 * b] - bb[4 * a + 1]));
-                const T gy = tmax(T(0), tmax(bb[4 * a + 2] - bb[4 * b + 3], bb[4 * b + 2] - bb[4 * a + 3]));
-                const T sg = P.d.sig[a == PK][b == PK] + sl;
-                if (fm(gx, gx, gy * gy) <= sg * sg) pb.set(pair_index(a, b));
-            }
-    }
-    // closed-form commit of column 50 of a contact-free step (eval() with j = 50 and zero offsets)
-    RGS_DEV void quiet_commit(T *st, const T *cmd) const {
-        const T tj = P.d.dt_col * T(kGrid);
-#pragma unroll
-        for (int e = 0; e < E; ++e) {
-            const LaneGK<T> gk = tab->e[e == PK][kGrid];
-#pragma unroll
-            for (int a = 0; a < 2; ++a) {
-                const T u = e == PK ? T(0) : cmd[2 * (e == PK ? 0 : e) + a];
-                const T w = st[4 * e + 2 + a] - u;
-                st[4 * e + a] = fm(w, gk.k, fm(u, tj, st[4 * e + a])) + T(0);
-                st[4 * e + 2 + a] = fm(w, gk.g, u);
-            }
-        }
-    }
-    // registers -> scratch record at the start of a step that has flagged items
-    RGS_DEV void spill(const T *st, const T *cmd, const T *bb) const {
-#pragma unroll
-        for (int e = 0; e < E; ++e) {
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                s.F(S::SP + 4 * e + c) = st[4 * e + c];
-                s.F(S::PRV + 4 * e + c) = st[4 * e + c];
-                s.F(S::OFF + 4 * e + c) = T(0);
-                s.F(S::BB + 4 * e + c) = bb[4 * e + c];
-            }
-            s.F(S::CMD + 2 * e) = e == PK ? T(0) : cmd[2 * (e == PK ? 0 : e)];
-            s.F(S::CMD + 2 * e + 1) = e == PK ? T(0) : cmd[2 * (e == PK ? 0 : e) + 1];
-            s.I(S::CS + e) = 0;
-            s.I(S::FL + e) = 0;
-        }
-    }
-    // column 50 of every body -> registers (:153-157)
-    RGS_DEV void commit_to(T *st) const {
-#ifdef RGS_COMMIT_LOOP
-#pragma unroll 1
-        for (int e = 0; e < E; ++e) {  // one copy of eval(): through the record, then into registers
-            T px, py, vx, vy;
-            eval(e, kGrid, px, py, vx, vy);
-            s.F(S::SP + 4 * e) = px; s.F(S::SP + 4 * e + 1) = py; s.F(S::SP + 4 * e + 2) = vx; s.F(S::SP + 4 * e + 3) = vy;
-        }
-#pragma unroll
-        for (int c = 0; c < 4 * E; ++c) st[c] = s.F(S::SP + c);
-#else
-#pragma unroll
-        for (int e = 0; e < E; ++e) eval(e, kGrid, st[4 * e], st[4 * e + 1], st[4 * e + 2], st[4 * e + 3]);
-#endif
-    }
-    RGS_DEV int step_regs(T *st, const T *cmd, double &sa, double &sb, long long *ev, double *dmg, long long live) const {
-        T bb[4 * E];
-        Bits<4 * E> wb;
-        Bits<NPAIR> pb;
-        head_flags(st, cmd, bb, wb, pb);
-        if (!(wb.any() || pb.any())) {
-            quiet_commit(st, cmd);
-            return 1;
-        }
-        spill(st, cmd, bb);
-        const int counter = event_loop(wb, pb, sa, sb, ev, dmg, live);
-        commit_to(st);
-        return counter;
-    }
 };
 
 // trajectory record [t, state (reference order), damage] after step k
@@ -1194,8 +1118,9 @@ RGS_DEV void write_traj_lane(const RunArgs &A, const LaneScratch<T, NT> &s, int6
     for (int d = 0; d < NP * NP; ++d) rec[1 + SREC + d] = A.damage[game * (NP * NP) + d];
 }
 
-// all n_steps of ONE game (the body of a lane).  Teams of up to 3: the state lives in registers
-// between steps (step_regs); larger teams keep it in the scratch record (step).
+// all n_steps of ONE game (the body of a lane).  The game lives in the lane's scratch record (shared memory)
+// for the whole launch; HBM is read once at the start and written once at the end (plus the command record every
+// `hold` steps and the optional strided trajectory).
 // kPolicy: the commands come from the on-device surrogate policy (rgs_policy.cuh), evaluated on the state at the
 // start of EVERY game-step (the reference calls the team methods once per step, py/MonteCarlo.py:37-46); a separate
 // instantiation, so that the open-loop kernels do not carry its code.
@@ -1203,56 +1128,33 @@ template <typename T, int NT, bool kPolicy = false>
 RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const LaneTab<T> *tab, const LaneScratch<T, NT> &s,
                                int64_t game) {
     constexpr int E = 2 * NT + 1, PK = 2 * NT, SREC = 2 + 4 * E, NP = 2 * NT;
-    // Measured on B200 (profiles/r01_ab_variants.md): the register form executes 11 % fewer instructions but its
-    // unrolled code (4576 vs 3440 SASS instructions) misses the instruction cache more (no_instruction stall 5.2
-    // vs 2.3 per issue): 1.82e9 vs 2.16e9 game-steps/s.  It stays available for the phased kernel and for A/B.
-#ifdef RGS_LANE_REG_STATE
-    constexpr bool kRegs = NT <= 3;
-#else
-    constexpr bool kRegs = false;
-#endif
     using S = LaneScratch<T, NT>;
     const LaneGame<T, NT> G(P, tab, s);
     double *srec = A.state + game * SREC;
-    T st[kRegs ? 4 * E : 1], cmd[kRegs ? 2 * NP : 1];
-    if constexpr (kRegs) {
-#pragma unroll
-        for (int slot = 0; slot < E; ++slot) {
-            const int e = slot == 0 ? PK : slot - 1;
-#pragma unroll
-            for (int c = 0; c < 4; ++c) st[4 * e + c] = T(srec[2 + 4 * slot + c]);
-        }
-#pragma unroll
-        for (int c = 0; c < 2 * NP; ++c) cmd[c] = T(0);
-    } else {
 #pragma unroll 1
-        for (int slot = 0; slot < E; ++slot) {
-            const int e = slot == 0 ? PK : slot - 1;
+    for (int slot = 0; slot < E; ++slot) {
+        const int e = slot == 0 ? PK : slot - 1;
 #pragma unroll
-            for (int c = 0; c < 4; ++c) {
-                const T v = T(srec[2 + 4 * slot + c]);
-                s.F(S::SP + 4 * e + c) = v;
-                s.F(S::PRV + 4 * e + c) = v;
-            }
-            s.F(S::CMD + 2 * e) = T(0);
-            s.F(S::CMD + 2 * e + 1) = T(0);
+        for (int c = 0; c < 4; ++c) {
+            const T v = T(srec[2 + 4 * slot + c]);
+            s.F(S::SP + 4 * e + c) = v;
+            s.F(S::PRV + 4 * e + c) = v;
         }
+        s.F(S::CMD + 2 * e) = T(0);
+        s.F(S::CMD + 2 * e + 1) = T(0);
     }
     double sa = srec[0], sb = srec[1];
     double t_clock = A.clock[game];
-    // The event record is updated from divergent code with run-time indices.  In global memory every lane's record
-    // is its own 128-byte line (32 lines per warp access); a thread-local copy is interleaved across the lanes.
-#ifndef RGS_EV_IN_GLOBAL
-    long long evloc[RGS_N_EVENTS];
-    {
-        const long long *g0 = A.events + game * RGS_N_EVENTS;
-#pragma unroll
-        for (int i = 0; i < RGS_N_EVENTS; ++i) evloc[i] = g0[i];
-    }
-    long long *gev = evloc;
-#else
+    // event record: the counters of this launch are 32-bit words of the scratch record (updated from divergent code
+    // with run-time indices), added to the game's int64 record at the end; the hash is carried over
     long long *gev = A.events + game * RGS_N_EVENTS;
-#endif
+#pragma unroll 1
+    for (int i = 0; i < RGS_N_EVENTS; ++i) s.I(S::EVC + i) = 0;
+    {
+        const unsigned long long h0 = (unsigned long long)gev[RGS_EV_HASH];
+        s.I(S::EVC + RGS_EV_HASH) = (int)(unsigned)h0;
+        s.I(S::EVC + 16) = (int)(unsigned)(h0 >> 32);
+    }
     double *dmg = A.damage + game * (NP * NP);
     long long live = gev[RGS_EV_LIVE_STEPS], loop_iters = gev[RGS_EV_LOOP_ITERS], decided = gev[RGS_EV_DECIDED_STEP];
     const T *actions = static_cast<const T *>(A.actions);
@@ -1263,221 +1165,54 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
     bool fetch = true;
     const bool logging = A.traj != nullptr && A.log_stride > 0;
     int64_t k = 0, log_left = A.log_stride;
-    auto log_now = [&](int64_t kk) {
-        if constexpr (kRegs) {
-#pragma unroll
-            for (int e = 0; e < E; ++e)
-#pragma unroll
-                for (int c = 0; c < 4; ++c) s.F(S::SP + 4 * e + c) = st[4 * e + c];
-        }
-        write_traj_lane<T, NT>(A, s, game, kk, t_clock, sa, sb);
-    };
 #pragma unroll 1
     for (; k < A.n_steps; ++k) {
         if (!(sa < wsc && sb < wsc)) break;  // undecided(), :57-60
-        if constexpr (kPolicy && !kRegs) {
+        if constexpr (kPolicy) {
             T u[2 * NP];
             surrogate_policy<T, NT>(P.d, A.pol, [&](int e, int c) { return s.F(S::SP + 4 * e + c); }, u);
 #pragma unroll
             for (int c = 0; c < 2 * NP; ++c) s.F(S::CMD + c) = u[c];
-        } else
-        if (fetch) {
+        } else if (fetch) {
             const int64_t ai = (A.synth || aidx < A.n_act) ? aidx : A.n_act - 1;
-            if constexpr (kRegs) {
 #pragma unroll 1
-                for (int c = 0; c < 2 * NP; ++c) {  // one copy of the generator; the select chain keeps cmd[] in registers
-                    const T v = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
-                                        : actions[game * A.act_game_stride + ai * (2 * NP) + c];
-#pragma unroll
-                    for (int c2 = 0; c2 < 2 * NP; ++c2)
-                        if (c2 == c) cmd[c2] = v;
-                }
-            } else {
-#pragma unroll 1
-                for (int c = 0; c < 2 * NP; ++c)
-                    s.F(S::CMD + c) = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
-                                              : actions[game * A.act_game_stride + ai * (2 * NP) + c];
-            }
+            for (int c = 0; c < 2 * NP; ++c)
+                s.F(S::CMD + c) = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
+                                          : actions[game * A.act_game_stride + ai * (2 * NP) + c];
             fetch = false;
         }
         if (++phase == A.hold) { phase = 0; ++aidx; fetch = true; }
-        if constexpr (kRegs) loop_iters += G.step_regs(st, cmd, sa, sb, gev, dmg, live);
-        else loop_iters += G.step(sa, sb, gev, dmg, live);
+        loop_iters += G.step(t_clock, sa, sb, dmg, live);
         t_clock += (double)P.d.dt;  // t_ += dt_ (:158), fp64 like the reference clock
-        ++live;
-        if (decided == 0 && !(sa < wsc && sb < wsc)) decided = live;
-        if (logging && --log_left == 0) {
-            log_left = A.log_stride;
-            log_now(k);
-        }
-    }
-    if (logging)  // frozen steps of a decided game (GameSim::run :121-123) repeat the frozen state
-        for (; k < A.n_steps; ++k)
-            if (--log_left == 0) { log_left = A.log_stride; log_now(k); }
-    srec[0] = sa;
-    srec[1] = sb;
-#pragma unroll
-    for (int slot = 0; slot < E; ++slot) {
-        const int e = slot == 0 ? PK : slot - 1;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) srec[2 + 4 * slot + c] = kRegs ? (double)st[kRegs ? 4 * e + c : 0] : (double)s.F(S::SP + 4 * e + c);
-    }
-    A.clock[game] = t_clock;
-    gev[RGS_EV_LIVE_STEPS] = live;
-    gev[RGS_EV_LOOP_ITERS] = loop_iters;
-    gev[RGS_EV_DECIDED_STEP] = decided;
-#ifndef RGS_EV_IN_GLOBAL
-    {
-        long long *g0 = A.events + game * RGS_N_EVENTS;
-#pragma unroll
-        for (int i = 0; i < RGS_N_EVENTS; ++i) g0[i] = evloc[i];
-    }
-#endif
-}
-
-// ---------------------------------------------------------------------------------------------------------
-// The same rollout with the WARP as the scheduling unit ("deferred event batching").  rollout_lane_game keeps the
-// 32 games of a warp in lock-step per game-step: every game-step the warp runs the contact-free head (32 lanes)
-// and then the event loop for the few lanes that have contacts (profiles/r01_ncu_lane_v7_full.md: 9.7 of 32
-// lanes active on average, the event path ~4 lanes wide).  Games are independent, so here a lane that meets a
-// contact PARKS in the event loop while the others go on with their next game-steps; the warp executes an event
-// iteration only when `batch` lanes are parked (or nobody is left to advance), and then all of them take it
-// together.  A lane that finishes its game stores it and loads the next one of its stride without waiting for
-// the rest of the warp.  Every game executes exactly the statements rollout_lane_game executes for it, in the
-// same order: results are bit-identical, only the interleaving between lanes differs.
-// ---------------------------------------------------------------------------------------------------------
-RGS_DEV unsigned lane_ballot(bool p) {
-#ifdef RGS_HOST_EMU
-    return p ? 1u : 0u;   // the emulator runs one lane at a time
-#else
-    return __ballot_sync(0xffffffffu, p);
-#endif
-}
-RGS_DEV int lane_popc(unsigned m) {
-#ifdef RGS_HOST_EMU
-    return __builtin_popcount(m);
-#else
-    return __popc(m);
-#endif
-}
-
-template <typename T, int NT>
-RGS_DEV void rollout_lane_warp(const FastParams<T> &P, const RunArgs &A, const LaneTab<T> *tab, const LaneScratch<T, NT> &s,
-                               int64_t game, const int64_t game_stride, const int batch) {
-    constexpr int E = 2 * NT + 1, PK = 2 * NT, SREC = 2 + 4 * E, NP = 2 * NT;
-    using S = LaneScratch<T, NT>;
-    using Game = LaneGame<T, NT>;
-    const Game G(P, tab, s);
-    enum : int { LOAD = 0, HEAD = 1, EVENT = 2, DONE = 3 };
-    int mode = game < A.n_games ? LOAD : DONE;   // lanes without a game still vote
-    // per game
-    double sa = 0.0, sb = 0.0, t_clock = 0.0;
-    long long evloc[RGS_N_EVENTS];
-    long long live = 0, loop_iters = 0, decided = 0;
-    int64_t aidx = 0, phase = 0, k = 0, log_left = 0;
-    bool fetch = true;
-    // per step
-    typename Game::EvState X;
-    typename Game::JamSnap J;
-    const T *actions = static_cast<const T *>(A.actions);
-    const double wsc = (double)P.d.winning_score;
-    const bool logging = A.traj != nullptr && A.log_stride > 0;
-    auto end_step = [&]() {   // the tail of rollout_lane_game's step loop
-        loop_iters += X.counter;
-        t_clock += (double)P.d.dt;
         ++live;
         if (decided == 0 && !(sa < wsc && sb < wsc)) decided = live;
         if (logging && --log_left == 0) {
             log_left = A.log_stride;
             write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb);
         }
-        ++k;
-    };
+    }
+    if (logging)  // frozen steps of a decided game (GameSim::run :121-123) repeat the frozen state
+        for (; k < A.n_steps; ++k)
+            if (--log_left == 0) { log_left = A.log_stride; write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb); }
+    srec[0] = sa;
+    srec[1] = sb;
 #pragma unroll 1
-    for (;;) {
-        const unsigned parked = lane_ballot(mode == EVENT);
-        const unsigned movers = lane_ballot(mode == LOAD || mode == HEAD);
-        if ((parked | movers) == 0u) break;
-        if (lane_popc(parked) >= batch || movers == 0u) {
-            if (mode == EVENT) {
-                if (G.event_iter(X, J, sa, sb, evloc, A.damage + game * (NP * NP), live)) {
-                    G.step_commit();
-                    end_step();
-                    mode = HEAD;
-                }
-            }
-            continue;
-        }
-        if (mode == LOAD) {
-            const double *srec = A.state + game * SREC;
+    for (int slot = 0; slot < E; ++slot) {
+        const int e = slot == 0 ? PK : slot - 1;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) srec[2 + 4 * slot + c] = (double)s.F(S::SP + 4 * e + c);
+    }
+    A.clock[game] = t_clock;
 #pragma unroll 1
-            for (int slot = 0; slot < E; ++slot) {
-                const int e = slot == 0 ? PK : slot - 1;
-#pragma unroll
-                for (int c = 0; c < 4; ++c) {
-                    const T v = T(srec[2 + 4 * slot + c]);
-                    s.F(S::SP + 4 * e + c) = v;
-                    s.F(S::PRV + 4 * e + c) = v;
-                }
-                s.F(S::CMD + 2 * e) = T(0);
-                s.F(S::CMD + 2 * e + 1) = T(0);
-            }
-            sa = srec[0]; sb = srec[1];
-            t_clock = A.clock[game];
-            const long long *g0 = A.events + game * RGS_N_EVENTS;
-#pragma unroll
-            for (int i = 0; i < RGS_N_EVENTS; ++i) evloc[i] = g0[i];
-            live = evloc[RGS_EV_LIVE_STEPS]; loop_iters = evloc[RGS_EV_LOOP_ITERS]; decided = evloc[RGS_EV_DECIDED_STEP];
-            aidx = A.synth ? A.step0 / A.hold : 0;
-            phase = A.synth ? A.step0 % A.hold : 0;
-            fetch = true;
-            k = 0; log_left = A.log_stride;
-            mode = HEAD;
-        }
-        if (mode == HEAD) {
-            if (k < A.n_steps && sa < wsc && sb < wsc) {  // undecided(), :57-60
-                if (fetch) {
-                    const int64_t ai = (A.synth || aidx < A.n_act) ? aidx : A.n_act - 1;
-#pragma unroll 1
-                    for (int c = 0; c < 2 * NP; ++c)
-                        s.F(S::CMD + c) = A.synth ? T(synth_action(A.seed, A.first_game + game, ai, c, A.u_max))
-                                                  : actions[game * A.act_game_stride + ai * (2 * NP) + c];
-                    fetch = false;
-                }
-                if (++phase == A.hold) { phase = 0; ++aidx; fetch = true; }
-                G.step_head(X.wb, X.pb);
-                if (X.wb.any() || X.pb.any()) {
-                    G.event_begin(X, J);
-                    mode = EVENT;
-                } else {
-                    X.counter = 1;
-                    G.step_commit();
-                    end_step();
-                }
-            } else {
-                if (logging)  // frozen steps of a decided game (GameSim::run :121-123) repeat the frozen state
-                    for (; k < A.n_steps; ++k)
-                        if (--log_left == 0) { log_left = A.log_stride; write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb); }
-                double *srec = A.state + game * SREC;
-                srec[0] = sa;
-                srec[1] = sb;
-#pragma unroll 1
-                for (int slot = 0; slot < E; ++slot) {
-                    const int e = slot == 0 ? PK : slot - 1;
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) srec[2 + 4 * slot + c] = (double)s.F(S::SP + 4 * e + c);
-                }
-                A.clock[game] = t_clock;
-                evloc[RGS_EV_LIVE_STEPS] = live;
-                evloc[RGS_EV_LOOP_ITERS] = loop_iters;
-                evloc[RGS_EV_DECIDED_STEP] = decided;
-                long long *g0 = A.events + game * RGS_N_EVENTS;
-#pragma unroll
-                for (int i = 0; i < RGS_N_EVENTS; ++i) g0[i] = evloc[i];
-                game += game_stride;
-                mode = game < A.n_games ? LOAD : DONE;
-            }
-        }
+    for (int i = 0; i < RGS_N_EVENTS; ++i) {
+        long long v;
+        if (i == RGS_EV_LIVE_STEPS) v = live;
+        else if (i == RGS_EV_LOOP_ITERS) v = loop_iters;
+        else if (i == RGS_EV_DECIDED_STEP) v = decided;
+        else if (i == RGS_EV_HASH)
+            v = (long long)(((unsigned long long)(unsigned)s.I(S::EVC + 16) << 32) | (unsigned)s.I(S::EVC + RGS_EV_HASH));
+        else v = gev[i] + (long long)s.I(S::EVC + i);
+        gev[i] = v;
     }
 }
 

@@ -4,8 +4,8 @@
 // Shared memory per CTA: the closed-form coefficient table + one scratch record per thread, laid
 // out word-major ([word][thread]) so that the run-time body indices of the event path never cause
 // a bank conflict (bank = lane) and never force per-thread arrays into local memory.
-#include <cstdlib>
-
+// Global memory per resident lane: LaneScratch::SCR_WORDS words (correctOverlap tracks + jam snapshot),
+// lane-interleaved inside a warp ([word][lane]); touched only by bodies that are corrected repeatedly.
 #include "rgs_lane.cuh"
 #include "rgs_host_params.h"
 #include "rgs_kernels.h"
@@ -13,11 +13,8 @@
 namespace rgs {
 
 template <typename T, int NT, int THREADS, bool kPolicy = false>
-#ifndef RGS_LANE_MINBLOCKS
-#define RGS_LANE_MINBLOCKS 1
-#endif
-__global__ void __launch_bounds__(THREADS, RGS_LANE_MINBLOCKS) rollout_lane_kernel(const __grid_constant__ FastParams<T> P,
-                                                               const __grid_constant__ RunArgs A, const int lanes, const int batch) {
+__global__ void __launch_bounds__(THREADS, 1) rollout_lane_kernel(const __grid_constant__ FastParams<T> P,
+                                                                  const __grid_constant__ RunArgs A, const int lanes) {
     // `lanes` = games per CTA.  It equals THREADS except in the one-warp instantiation used for small batches
     // (launch_lane_nt), where a CTA may carry fewer games than it has threads: a latency-bound batch finishes sooner
     // on many thin warps (less divergence per warp, more warps per scheduler) than on a few full ones.
@@ -33,17 +30,13 @@ __global__ void __launch_bounds__(THREADS, RGS_LANE_MINBLOCKS) rollout_lane_kern
         (&tab->e[0][0])[i].k = (&P.tab_k[0][0])[i];
     }
     __syncthreads();
-    const S s{fw + threadIdx.x, iw + threadIdx.x, per_cta};
-    const int64_t stride = (int64_t)gridDim.x * per_cta;
-#ifdef RGS_LANE_DEB
-    // warp-scheduled form: every thread of the warp votes, threads beyond per_cta own no game
-    const int64_t game = (int)threadIdx.x < per_cta ? (int64_t)blockIdx.x * per_cta + threadIdx.x : A.n_games;
-    rollout_lane_warp<T, NT>(P, A, tab, s, game, stride, batch);
-#else
     if ((int)threadIdx.x >= per_cta) return;
+    const size_t warp = ((size_t)blockIdx.x * THREADS + threadIdx.x) >> 5;
+    T *scr = static_cast<T *>(A.lane_scratch) + warp * ((size_t)S::SCR_WORDS * 32) + (threadIdx.x & 31);
+    const S s{fw + threadIdx.x, iw + threadIdx.x, per_cta, scr, 32};
+    const int64_t stride = (int64_t)gridDim.x * per_cta;
     for (int64_t game = (int64_t)blockIdx.x * per_cta + threadIdx.x; game < A.n_games; game += stride)
         rollout_lane_game<T, NT, kPolicy>(P, A, tab, s, game);
-#endif
 }
 
 template <typename T, int NT>
@@ -52,40 +45,46 @@ constexpr size_t lane_smem_bytes(int threads) {
            ((size_t)LaneScratch<T, NT>::NF * sizeof(T) + (size_t)LaneScratch<T, NT>::NI * sizeof(int)) * threads;
 }
 
-template <typename T, int NT, int kThreads, bool kPolicy = false>
-static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count,
-                                     int lanes = kThreads) {
-    size_t smem = lane_smem_bytes<T, NT>(lanes);
-#ifdef RGS_EXP_ONLY_2V2
-    if (const char *pad = std::getenv("RGS_EXP_SMEM_PAD")) smem += (size_t)std::atoi(pad);  // occupancy sensitivity experiments
-#endif
+// CTA size: measured on B200 (profiles/r01_ab_variants.md), 128 lanes per CTA (3 CTAs = 12 warps per SM for
+// 2v2 fp32) run 10 % faster than 64 (7 CTAs); 256 and 512 are level with 128, 192 / 320 / 384 clearly worse.
+// Records too large for two 128-lane CTAs per SM keep 64.
+template <typename T, int NT>
+constexpr int lane_big_threads() { return lane_smem_bytes<T, NT>(128) <= 110 * 1024 ? 128 : 64; }
+
+constexpr int kSmallWarpsPerSm = 7;   // one-warp CTAs per SM aimed at by the small-batch path (see launch_lane_nt)
+
+template <typename T, int NT, int kThreads, bool kPolicy>
+static cudaError_t lane_resident_ctas(int lanes, int *per_sm) {
+    const size_t smem = lane_smem_bytes<T, NT>(lanes);
     auto kern = rollout_lane_kernel<T, NT, kThreads, kPolicy>;
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(per_sm, kern, kThreads, smem);
+    if (err == cudaSuccess && *per_sm < 1) *per_sm = 1;
+    return err;
+}
+
+template <typename T, int NT, int kThreads, bool kPolicy = false>
+static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count,
+                                     int lanes = kThreads) {
     int per_sm = 0;
-    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kThreads, smem);
+    cudaError_t err = lane_resident_ctas<T, NT, kThreads, kPolicy>(lanes, &per_sm);
     if (err != cudaSuccess) return err;
-    if (per_sm < 1) per_sm = 1;
     int64_t blocks = (A.n_games + lanes - 1) / lanes;
     const int64_t cap = (int64_t)sm_count * per_sm;  // persistent grid: resident CTAs x SM count
     if (blocks > cap) blocks = cap;  // (equalising the rounds per lane was measured: no gain, profiles/r01_ab_variants.md)
     if (blocks < 1) blocks = 1;
-    int batch = 16;  // lanes parked in the event loop before the warp runs an event iteration (RGS_LANE_DEB builds)
-    if (const char *e = std::getenv("RGS_DEB_BATCH")) batch = std::atoi(e);
-    kern<<<(unsigned)blocks, kThreads, smem, stream>>>(P, A, lanes, batch);
+    const size_t need = (size_t)blocks * kThreads * LaneScratch<T, NT>::SCR_WORDS * sizeof(T);
+    if (!A.lane_scratch || A.lane_scratch_bytes < need) return cudaErrorInvalidValue;
+    rollout_lane_kernel<T, NT, kThreads, kPolicy><<<(unsigned)blocks, kThreads, lane_smem_bytes<T, NT>(lanes), stream>>>(P, A, lanes);
     return cudaGetLastError();
 }
 
-// CTA size: measured on B200 (profiles/r01_ab_variants.md), 128 lanes per CTA (3 CTAs = 12 warps per SM for
-// 2v2 fp32) run 10 % faster than 64 (7 CTAs); 256 and 512 are level with 128, 192 / 320 / 384 clearly worse.
-// Records too large for two 128-lane CTAs per SM keep 64; batches smaller than one 128-lane CTA per SM (the
-// K3 sampler's 4096 candidates) use one-warp CTAs carrying only a few games each, so that they spread over all SMs.
+// Batches smaller than one big CTA per SM (the K3 sampler's 4096 candidates) use one-warp CTAs carrying only a few
+// games each, so that they spread over all SMs.
 template <typename T, int NT>
 static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count) {
-#ifdef RGS_LANE_THREADS
-    return launch_lane_sized<T, NT, RGS_LANE_THREADS>(P, A, stream, sm_count);
-#else
-    constexpr int kBig = lane_smem_bytes<T, NT>(128) <= 110 * 1024 ? 128 : 64;
+    constexpr int kBig = lane_big_threads<T, NT>();
     if (A.synth == 2) {  // closed loop on the on-device policy: instantiated for the reference's 2v2 only
         if constexpr (NT == 2) return launch_lane_sized<T, NT, kBig, true>(P, A, stream, sm_count);
         else return cudaErrorNotSupported;
@@ -94,40 +93,58 @@ static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cuda
         // games per one-warp CTA: aim at 7 warps per SM.  Measured on the 4096 x 50-step sampler tick
         // (profiles/r01_configs.json): 32 lanes 2.36 ms, 8 lanes 1.84, 4 lanes (6.9 warps/SM) 1.54, 2 lanes 1.87,
         // 1 lane (28 warps/SM, instruction-fetch-bound) 2.64.
-        int lanes = (int)((A.n_games + (int64_t)sm_count * 7 - 1) / ((int64_t)sm_count * 7));
-        if (const char *e = std::getenv("RGS_SMALL_LANES")) lanes = std::atoi(e);  // tuning knob
+        int lanes = (int)((A.n_games + (int64_t)sm_count * kSmallWarpsPerSm - 1) / ((int64_t)sm_count * kSmallWarpsPerSm));
         if (lanes < 1) lanes = 1;
         if (lanes > 32) lanes = 32;
         return launch_lane_sized<T, NT, 32>(P, A, stream, sm_count, lanes);
     }
     return launch_lane_sized<T, NT, kBig>(P, A, stream, sm_count);
-#endif
 }
 
-template <typename T>
-static cudaError_t launch_lane(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count) {
-    const FastParams<T> P = make_fast_params<T>(p);
+// upper bound of the scratch any launch of this (T, NT) can need on a device with sm_count SMs
+template <typename T, int NT>
+static cudaError_t lane_scratch_nt(int sm_count, size_t *bytes) {
+    constexpr int kBig = lane_big_threads<T, NT>();
+    int per_sm = 0;
+    cudaError_t err = lane_resident_ctas<T, NT, kBig, false>(kBig, &per_sm);
+    if (err != cudaSuccess) return err;
+    int64_t threads = (int64_t)per_sm * kBig;
+    if constexpr (NT == 2) {
+        err = lane_resident_ctas<T, NT, kBig, true>(kBig, &per_sm);
+        if (err != cudaSuccess) return err;
+        if ((int64_t)per_sm * kBig > threads) threads = (int64_t)per_sm * kBig;
+    }
+    // small-batch path: at most kSmallWarpsPerSm (+1 for the rounding of games per CTA) one-warp CTAs per SM
+    if ((int64_t)(kSmallWarpsPerSm + 1) * 32 > threads) threads = (int64_t)(kSmallWarpsPerSm + 1) * 32;
+    *bytes = (size_t)sm_count * (size_t)threads * LaneScratch<T, NT>::SCR_WORDS * sizeof(T);
+    return cudaSuccess;
+}
+
+template <typename T, typename F>
+static cudaError_t by_team(int n_team, F &&f) {
     switch (n_team) {
-#ifndef RGS_EXP_ONLY_2V2
-    case 1: return launch_lane_nt<T, 1>(P, A, stream, sm_count);
-#endif
-    case 2: return launch_lane_nt<T, 2>(P, A, stream, sm_count);
-#ifndef RGS_EXP_ONLY_2V2
-    case 3: return launch_lane_nt<T, 3>(P, A, stream, sm_count);
-    case 4: return launch_lane_nt<T, 4>(P, A, stream, sm_count);
-    case 5: return launch_lane_nt<T, 5>(P, A, stream, sm_count);
-    case 6: return launch_lane_nt<T, 6>(P, A, stream, sm_count);
-    case 7: return launch_lane_nt<T, 7>(P, A, stream, sm_count);
-#endif
+    case 1: return f(std::integral_constant<int, 1>{});
+    case 2: return f(std::integral_constant<int, 2>{});
+    case 3: return f(std::integral_constant<int, 3>{});
+    case 4: return f(std::integral_constant<int, 4>{});
+    case 5: return f(std::integral_constant<int, 5>{});
+    case 6: return f(std::integral_constant<int, 6>{});
+    case 7: return f(std::integral_constant<int, 7>{});
     default: return cudaErrorInvalidValue;
     }
 }
 
 cudaError_t launch_rollout_lane_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count) {
-    return launch_lane<float>(n_team, p, A, stream, sm_count);
+    const FastParams<float> P = make_fast_params<float>(p);
+    return by_team<float>(n_team, [&](auto nt) { return launch_lane_nt<float, decltype(nt)::value>(P, A, stream, sm_count); });
 }
 cudaError_t launch_rollout_lane_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count) {
-    return launch_lane<double>(n_team, p, A, stream, sm_count);
+    const FastParams<double> P = make_fast_params<double>(p);
+    return by_team<double>(n_team, [&](auto nt) { return launch_lane_nt<double, decltype(nt)::value>(P, A, stream, sm_count); });
+}
+cudaError_t lane_scratch_bytes(int n_team, int fp64, int sm_count, size_t *bytes) {
+    if (fp64) return by_team<double>(n_team, [&](auto nt) { return lane_scratch_nt<double, decltype(nt)::value>(sm_count, bytes); });
+    return by_team<float>(n_team, [&](auto nt) { return lane_scratch_nt<float, decltype(nt)::value>(sm_count, bytes); });
 }
 
 }  // namespace rgs

@@ -1,6 +1,6 @@
 // tests/emu/emu_rollout.cpp -- TEST INFRASTRUCTURE ONLY (never on the product path).
 //
-// Compiles the product's kernel-body headers (robo_game_sim_b200/csrc/rgs_exact.cuh, rgs_fast.cuh)
+// Compiles the product's kernel-body headers (robo_game_sim_b200/csrc/rgs_exact.cuh, rgs_lane.cuh)
 // with g++ against the fiber warp emulator (warp_emu.h) so their control flow and arithmetic can be
 // checked against the oracle in this GPU-less container.  The resulting tests/emu/librgs_emu.so is
 // loaded by tests/ only; robo_game_sim_b200 never loads it and has no CPU path.
@@ -9,7 +9,6 @@
 #include "../../robo_game_sim_b200/csrc/rgs_exact.cuh"
 #include "../../robo_game_sim_b200/csrc/rgs_fast.cuh"
 #include "../../robo_game_sim_b200/csrc/rgs_lane.cuh"
-#include "../../robo_game_sim_b200/csrc/rgs_phase.cuh"
 #include "../../robo_game_sim_b200/csrc/rgs_host_params.h"
 
 #include <memory>
@@ -25,17 +24,7 @@ void run_exact(const rgs_params &p, const rgs::RunArgs &A) {
 }
 
 template <typename T, int NT>
-void run_fast(const rgs_params &p, const rgs::RunArgs &A) {
-    auto W = std::make_unique<rgs::WarpSlice<T, NT>>();
-    auto tab = std::make_unique<rgs::FastTables<T>>();
-    const rgs::FastParams<T> P = rgs::make_fast_params<T>(p);
-    for (int ty = 0; ty < 2; ++ty)
-        for (int i = 0; i < rgs::kCols; ++i) { tab->g[ty][i] = P.tab_g[ty][i]; tab->k[ty][i] = P.tab_k[ty][i]; }
-    emu::run_warp([&](int lane) { rgs::rollout_fast_warp<T, NT>(P, A, W.get(), tab.get(), lane, 0, 1); });
-}
-
-template <typename T, int NT>
-void run_lane(const rgs_params &p, const rgs::RunArgs &A, bool warp_sched = false) {
+void run_lane(const rgs_params &p, const rgs::RunArgs &A) {
     using S = rgs::LaneScratch<T, NT>;
     auto tab = std::make_unique<rgs::LaneTab<T>>();
     const rgs::FastParams<T> P = rgs::make_fast_params<T>(p);
@@ -43,73 +32,19 @@ void run_lane(const rgs_params &p, const rgs::RunArgs &A, bool warp_sched = fals
         for (int i = 0; i < rgs::kCols; ++i) { tab->e[ty][i].g = P.tab_g[ty][i]; tab->e[ty][i].k = P.tab_k[ty][i]; }
     T fw[S::NF];
     int iw[S::NI];
-    S s{fw, iw, 1};
+    std::vector<T> scr(S::SCR_WORDS);   // the lane's global scratch area (correctOverlap tracks + jam snapshot)
+    S s{fw, iw, 1, scr.data(), 1};
     if (A.synth == 2) {   // closed loop on the on-device surrogate policy (instantiated for 2v2, like the library)
         if constexpr (NT == 2)
             for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT, true>(P, A, tab.get(), s, g);
-    } else if (warp_sched) rgs::rollout_lane_warp<T, NT>(P, A, tab.get(), s, 0, 1, 16);  // one lane walks all the games
-    else for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT>(P, A, tab.get(), s, g);
-}
-
-// The phased block kernel (rgs_phase.cuh), one block of `n_threads` slots; the threads of a phase are
-// stepped one after the other, the barriers of rollout_phase_kernel are the ends of the loops.
-// RGS_EMU_PHASE="threads,records,item_capacity" overrides the geometry (pool-exhaustion and
-// list-overflow paths).
-template <typename T, int NT>
-void run_phase(const rgs_params &p, const rgs::RunArgs &A) {
-    using Sh = rgs::PhaseShared<T, NT>;
-    int n_threads = 64, n_rec = 32, cap = 128;
-    if (const char *g = std::getenv("RGS_EMU_PHASE")) std::sscanf(g, "%d,%d,%d", &n_threads, &n_rec, &cap);
-    const rgs::FastParams<T> P = rgs::make_fast_params<T>(p);
-    std::vector<unsigned char> raw(Sh::bytes(n_rec, cap) + 16);
-    unsigned char *base = raw.data() + ((16 - (reinterpret_cast<uintptr_t>(raw.data()) & 15)) & 15);
-    Sh sh;
-    sh.carve(base, n_rec, cap);
-    auto *tab = reinterpret_cast<rgs::LaneTab<T> *>(base);
-    for (int ty = 0; ty < 2; ++ty)
-        for (int i = 0; i < rgs::kCols; ++i) { tab->e[ty][i].g = P.tab_g[ty][i]; tab->e[ty][i].k = P.tab_k[ty][i]; }
-    for (int i = 0; i < n_rec; ++i) sh.free_stack[i] = i;
-    for (int i = 0; i < 8; ++i) sh.ctr[i] = i == Sh::FREE_TOP ? n_rec : 0;
-    const rgs::PhaseKernel<T, NT> K(P, A, sh);
-    std::vector<rgs::PhaseSlot<T, NT>> ts(n_threads);
-    for (int t = 0; t < n_threads; ++t) K.init_slot(ts[t], t);
-    auto any_rec = [&] { for (auto &s : ts) if (s.rec >= 0) return true; return false; };
-    auto all_done = [&] { for (auto &s : ts) if (!K.slot_done(s)) return false; return true; };
-    for (;;) {
-        for (int t = 0; t < n_threads; ++t) K.head(ts[t], n_threads);
-        bool more = any_rec();
-        for (int t = 0; t < n_threads; ++t) K.release_held(ts[t]);
-        if (!more) {
-            if (all_done()) break;
-            continue;
-        }
-        for (int r = 0; r < rgs::kPhaseRounds && more; ++r) {
-            for (int t = 0; t < n_threads; ++t) K.search(t, n_threads);
-            sh.ctr[Sh::N_WALL] = 0;
-            sh.ctr[Sh::N_PAIR] = 0;
-            for (int t = 0; t < n_threads; ++t) K.pop_phase(ts[t]);
-            for (int t = 0; t < n_threads; ++t) K.resolve_phase(t, n_threads);
-            more = any_rec();
-            sh.ctr[Sh::N_WALL_EV] = 0;
-            sh.ctr[Sh::N_PAIR_EV] = 0;
-        }
-    }
+    } else for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT>(P, A, tab.get(), s, g);
 }
 
 template <int NT>
 void dispatch(const rgs_params &p, const rgs::RunArgs &A) {
-    // the FAST modes run the lane body, as librgs_b200.so does; RGS_K2_WARP=1 selects the superseded
-    // warp-per-game body there and here (33 / 66 always mean the lane body: A/B scripts)
-    const char *w = std::getenv("RGS_K2_WARP");
-    const bool warp_k2 = w && w[0] == '1';
+    // the FAST modes run the lane body, as librgs_b200.so does
     if (p.mode == RGS_MODE_EXACT_F64) run_exact<NT>(p, A);
-    else if (p.mode == RGS_MODE_FAST_F32 && warp_k2) run_fast<float, NT>(p, A);
-    else if (p.mode == RGS_MODE_FAST_F64 && warp_k2) run_fast<double, NT>(p, A);
-    else if (p.mode == 34) { if constexpr (NT <= 3) run_phase<float, NT>(p, A); }
-    else if (p.mode == 67) { if constexpr (NT <= 3) run_phase<double, NT>(p, A); }
-    else if (p.mode == 35) run_lane<float, NT>(p, A, true);    // 35 / 68: the warp-scheduled lane rollout (rollout_lane_warp)
-    else if (p.mode == 68) run_lane<double, NT>(p, A, true);
-    else if (p.mode == RGS_MODE_FAST_F32 || p.mode == 33) run_lane<float, NT>(p, A);
+    else if (p.mode == RGS_MODE_FAST_F32) run_lane<float, NT>(p, A);
     else run_lane<double, NT>(p, A);
 }
 

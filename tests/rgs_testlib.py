@@ -236,7 +236,7 @@ def emu_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, events
         rc = lib.emu_rollout(C.byref(p), n, _ptr(state), _ptr(t), _ptr(damage), _ptr(events, C.c_int64), None, 1, hold,
                              0, n_steps, log_stride, _ptr(traj), 1, seed, first_game, step0, u_max)
     else:
-        dt = np.float32 if pd["mode"] in (MODE_FAST_F32, 33, 34, 35) else np.float64
+        dt = np.float32 if pd["mode"] == MODE_FAST_F32 else np.float64
         actions = np.ascontiguousarray(actions, dtype=dt)
         shared = actions.ndim == 3
         n_act = actions.shape[0] if shared else actions.shape[1]

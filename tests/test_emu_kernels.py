@@ -1,4 +1,4 @@
-"""CPU suite, part 2: the PRODUCT's kernel bodies (robo_game_sim_b200/csrc/rgs_exact.cuh, rgs_fast.cuh)
+"""CPU suite, part 2: the PRODUCT's kernel bodies (robo_game_sim_b200/csrc/rgs_exact.cuh, rgs_lane.cuh)
 compiled with g++ on the fiber warp emulator (tests/emu) and compared with the oracle.  This checks
 the warp-level control flow (ballots, shuffles, lane roles) and the arithmetic of the very source
 nvcc compiles for sm_100a; the -m gpu tests repeat the comparison on the real kernels."""
@@ -67,17 +67,65 @@ def test_on_chip_synth_commands_equal_tensor_commands():
 
 
 def test_fast_formulation_fp64_tracks_oracle():
-    """K2's closed-form formulation in fp64: event-for-event identical to the oracle except where the
-    reference's own absolute-time rounding decides (jammed bodies, tau = 0 events)."""
-    pd, s0, acts = _s0(32, 100, 10, seed=3)
-    o = tl.oracle_rollout(pd, s0, acts, 100, 10)
+    """K2's closed-form formulation in fp64 (absolute clock like the reference): event-for-event identical to the
+    UNMODIFIED oracle over 200 steps except where rounding decides a resting contact (measured: 99.8 % of 1000 games,
+    tools/k2_fidelity.py --rollout)."""
+    pd, s0, acts = _s0(200, 200, 10, seed=3)
+    o = tl.oracle_rollout(pd, s0, acts, 200, 10)
     pf = dict(pd, mode=tl.MODE_FAST_F64)
-    e = tl.emu_rollout(pf, s0, acts, 100, 10)
+    e = tl.emu_rollout(pf, s0, acts, 200, 10)
     same = o["events"][:, tl.EV["HASH"]] == e["events"][:, tl.EV["HASH"]]
-    assert same.mean() >= 0.9
+    assert same.mean() >= 0.985
     assert np.array_equal(o["events"][same][:, :14], e["events"][same][:, :14])
+    assert np.array_equal(o["events"][same][:, 15], e["events"][same][:, 15])   # correctOverlap fixes too
     assert np.abs(o["state"] - e["state"])[same].max() < 1e-3   # rounding noise amplified by impacts
     assert np.median(np.abs(o["state"] - e["state"])[same].max(1)) < 1e-8
+
+
+def _single_step_mismatch(pd, n, steps, hold=10, seed=42, umax=10.0):
+    """Every state of an oracle rollout stepped ONCE by the oracle and by K2's fp64 instantiation (clock 0 on both
+    sides): (steps compared, steps whose event hash differs, hash-identical steps with a state error > 1e-6)."""
+    nt = pd["players_per_team"]
+    x0, acts = tl.synth_inputs(seed, 0, n, nt, (steps + hold - 1) // hold, u_max=umax)
+    s0 = tl.oracle_reset(pd, x0)
+    o = tl.oracle_rollout(pd, s0, acts, steps, hold, traj=True)
+    before = np.concatenate([s0[:, None], o["traj"][:, :-1]], axis=1).reshape(n * steps, -1)
+    a = np.repeat(acts, hold, axis=1)[:, :steps].reshape(n * steps, 1, 2 * nt, 2)
+    ro = tl.oracle_rollout(pd, before, a, 1, 1)
+    re = tl.emu_rollout(dict(pd, mode=tl.MODE_FAST_F64), before, a, 1, 1)
+    same = ro["events"][:, tl.EV["HASH"]] == re["events"][:, tl.EV["HASH"]]
+    err = np.abs(ro["state"] - re["state"]).max(1)
+    assert np.array_equal(ro["events"][same], re["events"][same])
+    assert ro["events"][:, 2:8].sum() > 0.02 * n * steps
+    return n * steps, int((~same).sum()), int((same & (err > 1e-6)).sum())
+
+
+@pytest.mark.parametrize("dt,tau_puck,tau_player,pm,km", [(0.02, 0.1, 0.5, 1.0, 0.5), (0.05, 1.0, 0.5, 1.0, 0.5),
+                                                          (0.1, 0.1, 0.5, 1.0, 0.5), (0.2, 0.1, 0.5, 1.0, 0.5),
+                                                          (0.2, 1.0, 0.2, 2.0, 0.1)])
+def test_fast_formulation_single_step_sweep(dt, tau_puck, tau_player, pm, km):
+    """Advisor finding of round 1: with one correctOverlap offset per body K2 departed from the reference on ordinary
+    wall contacts as dt grew (16 % of the steps at dt = 0.2).  With the cumulative per-column offsets (tracks) the
+    re-synced single-step mismatch rate is below 1e-3 and no hash-identical step has a state error, for every dt,
+    tau and mass set swept here (measured: 0 of 12 000 each, tools/k2_fidelity.py)."""
+    pd = tl.default_params(winning_score=1 << 30, dt=dt, tau_puck=tau_puck, tau_player=tau_player, player_mass=pm, puck_mass=km)
+    total, mism, bad = _single_step_mismatch(pd, 100, 40)
+    assert mism <= 1e-3 * total and bad == 0
+
+
+@pytest.mark.parametrize("n_team", [1, 3, 4, 7])
+def test_fast_formulation_nvn_tracks_oracle(n_team):
+    """K2 for team sizes other than 2 against the n-v-n oracle: re-synced single steps at dt = 0.1 (contact-heavy)
+    and a 100-step rollout at the default dt."""
+    pd = tl.default_params(n_team=n_team, winning_score=1 << 30, dt=0.1)
+    total, mism, bad = _single_step_mismatch(pd, 40, 40)
+    assert mism <= 1e-3 * total and bad == 0
+    pd, s0, acts = _s0(48, 100, 10, n_team=n_team, seed=9)
+    o = tl.oracle_rollout(pd, s0, acts, 100, 10)
+    e = tl.emu_rollout(dict(pd, mode=tl.MODE_FAST_F64), s0, acts, 100, 10)
+    same = o["events"][:, tl.EV["HASH"]] == e["events"][:, tl.EV["HASH"]]
+    assert same.mean() >= 0.95
+    assert np.array_equal(o["events"][same][:, :14], e["events"][same][:, :14])
 
 
 def test_fast_fp32_contact_free_and_first_contacts():
@@ -103,52 +151,3 @@ def test_fast_kernel_goal_and_freeze(golden):
         assert e["t"][0] == pytest.approx(0.25)
 
 
-# ---- K2 phased block kernel (rgs_phase.cuh): same bits as the one-lane-per-game body ----
-MODE_PHASE_F32, MODE_PHASE_F64 = 34, 67   # emulator-only selectors (librgs_b200.so picks the kernel itself)
-
-
-@pytest.mark.parametrize("geometry", [None, "64,4,8", "32,1,1", "7,3,2", "256,128,512"])
-@pytest.mark.parametrize("n_team", [1, 2, 3])
-def test_phase_kernel_equals_lane_kernel(monkeypatch, geometry, n_team):
-    """Block-compacted schedule vs one lane per game: every state double, clock, damage, event record
-    (incl. the order-sensitive event hash) and trajectory record identical, fp32 and fp64, also
-    when the record pool runs dry (slots retry the step) and the item lists overflow (items searched
-    on the spot), for any block size."""
-    if geometry:
-        monkeypatch.setenv("RGS_EMU_PHASE", geometry)
-    n, steps, hold = (600 if n_team == 2 else 150), 120, 10
-    x0, acts = tl.synth_inputs(5, 0, n, n_team, steps // hold)
-    s0 = tl.oracle_reset(tl.default_params(n_team=n_team), x0)
-    for lane_mode, phase_mode in ((tl.MODE_FAST_F32, MODE_PHASE_F32), (tl.MODE_FAST_F64, MODE_PHASE_F64)):
-        a = tl.emu_rollout(tl.default_params(n_team=n_team, mode=lane_mode, winning_score=1), s0, acts, steps, hold, log_stride=30)
-        b = tl.emu_rollout(tl.default_params(n_team=n_team, mode=phase_mode, winning_score=1), s0, acts, steps, hold, log_stride=30)
-        _assert_same(a, b)
-        assert np.array_equal(a["traj"], b["traj"])
-        assert a["events"][:, 2:8].sum() > 500 and a["events"][:, tl.EV["DECIDED_STEP"]].any()
-
-
-def test_phase_kernel_synth_and_resume():
-    pd = tl.default_params(mode=MODE_PHASE_F32)
-    x0, acts = tl.synth_inputs(77, 123, 40, 2, 6)
-    s0 = tl.oracle_reset(tl.default_params(), x0)
-    a = tl.emu_rollout(pd, s0, acts, 60, 10)
-    b = tl.emu_rollout(pd, s0, None, 60, 10, synth=(77, 123, 0, 10.0))
-    _assert_same(a, b)
-    h = tl.emu_rollout(pd, s0, acts[:, :3], 30, 10)
-    c = tl.emu_rollout(pd, h["state"], acts[:, 3:], 30, 10, t=h["t"], damage=h["damage"], events=h["events"])
-    _assert_same(a, c)
-
-
-@pytest.mark.parametrize("n_team,n,steps", [(2, 400, 120), (1, 100, 60), (4, 60, 40)])
-def test_warp_scheduled_rollout_equals_lane_rollout(n_team, n, steps):
-    """rollout_lane_warp (event loop cut at its iteration boundary, games loaded / stored inside the scheduling loop;
-    A/B build -DRGS_LANE_DEB, emulator modes 35 / 68) executes the statements of rollout_lane_game per game: the
-    results must be identical bit for bit, including the strided trajectory log and a resumed rollout."""
-    x0, acts = tl.synth_inputs(5, 0, n, n_team, steps // 10)
-    s0 = tl.oracle_reset(tl.default_params(n_team=n_team), x0)
-    for lane_mode, warp_mode in ((tl.MODE_FAST_F32, 35), (tl.MODE_FAST_F64, 68)):
-        a = tl.emu_rollout(tl.default_params(n_team=n_team, mode=lane_mode), s0, acts, steps, 10, log_stride=20)
-        b = tl.emu_rollout(tl.default_params(n_team=n_team, mode=warp_mode), s0, acts, steps, 10, log_stride=20)
-        _assert_same(a, b)
-        assert np.array_equal(a["traj"], b["traj"])
-        assert a["events"][:, 2:8].sum() > 50

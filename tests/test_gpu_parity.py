@@ -3,8 +3,9 @@ against the oracle on the same seeded inputs, against the committed golden fixtu
 BASELINE.json's full sizes -- through size-independent properties.
 
 Bars: fp64 parity mode (K1) bit-exact on every state double, clock, damage and event record;
-fast fp64 (K2 formulation) event-identical except where the reference's own absolute-time rounding
-decides; fast fp32 (K2) statistically equal to the oracle's Monte Carlo distributions.
+fast fp64 (K2 formulation, absolute clock) event-identical to the oracle except where rounding decides a
+resting contact (measured rates in DESIGN.md section 4); fast fp32 (K2) statistically equal to the reference's
+Monte Carlo score distribution (committed fixture tests/golden/mc_hist_2v2.npz).
 """
 import ctypes as C
 import os
@@ -205,65 +206,146 @@ def test_resume_synth_stats_and_host_entry(rgs):
 
 # ------------------------------------------------------------------ K2: throughput formulation
 def test_fast64_tracks_oracle(rgs):
-    n, steps, hold = 4096, 100, 10
+    """K2's formulation in fp64 against the UNMODIFIED oracle (absolute clock) over 200 steps.  Measured
+    (tools/k2_fidelity.py): 99.8 % of the games event-hash-identical; the residue is rounding
+    deciding a resting contact.  On the hash-identical games every integer outcome is equal."""
+    n, steps, hold = 4096, 200, 10
     pd = tl.default_params(winning_score=3)
     x0, acts = tl.synth_inputs(42, 0, n, 2, steps // hold)
     o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), acts, steps, hold)
     _, g = _gpu_rollout(rgs, "fast64", pd, x0, acts, steps, hold)
     same = o["events"][:, 14] == g["events"][:, 14]
-    assert same.mean() > 0.95
+    assert same.mean() >= 0.99
     assert np.array_equal(o["events"][same][:, :14], g["events"][same][:, :14])
+    assert np.array_equal(o["events"][same][:, 15], g["events"][same][:, 15])
+    assert np.array_equal(o["state"][same][:, :2], g["state"][same][:, :2])
     assert np.median(np.abs(o["state"] - g["state"])[same].max(1)) < 1e-8
+    assert np.abs(o["damage"] - g["damage"])[same].max() < 1e-6
     # and the emulator build of the same source gives the same bits as the GPU
     e = tl.emu_rollout(dict(pd, mode=tl.MODE_FAST_F64), tl.oracle_reset(pd, x0[:64]), acts[:64], steps, hold)
     assert np.array_equal(e["state"], g["state"][:64]) and np.array_equal(e["events"], g["events"][:64])
 
 
-def test_phase_kernel_equals_lane_kernel_on_gpu(rgs, monkeypatch):
-    """The block-compacted K2 (RGS_K2_LANE=0) and the one-lane-per-game K2 (default) give the same bits
-    for every game of a 300k-game batch, fp32 and fp64, with trajectory logging and on-chip commands."""
-    for mode, n, steps in (("fast", 300_000, 100), ("fast64", 60_000, 60)):
-        outs = []
-        for lane in ("0", "1"):
-            monkeypatch.setenv("RGS_K2_LANE", lane)
-            sim = rgs.BatchedGameSim(n, mode=mode, winning_score=2)
-            x0, _ = rgs.synth_inputs(n, 1, seed=5, dtype=sim.action_dtype)
-            sim.reset(x0_ball=x0)
-            traj = sim.run_synth(5, steps, hold=10, log_stride=50 if mode == "fast" else 0)
-            outs.append((sim.state(), sim.time(), sim.damage(), sim.events(), traj))
-        for a, b in zip(*outs):
-            assert (a is None and b is None) or torch.equal(a, b)
-        ev = outs[0][3]
-        assert int(ev[:, 2:8].sum()) > 0.1 * n * steps
+def _gpu_single_steps(rgs, mode, pd, before, acts1):
+    """One game-step from every state record of `before` [m, 2+4E] with commands acts1 [m, 1, 2n, 2]."""
+    m = before.shape[0]
+    kw = {k: pd[k] for k in ("dt", "winning_score", "tau_puck", "tau_player", "player_mass", "puck_mass")}
+    sim = rgs.BatchedGameSim(m, mode=mode, players_per_team=pd["players_per_team"], **kw)
+    sim.reset(state0=torch.from_numpy(before).cuda())
+    sim.run(torch.from_numpy(np.ascontiguousarray(acts1)).to(sim.action_dtype).cuda(), n_steps=1, hold=1)
+    return dict(state=sim.state().cpu().numpy(), events=sim.events().cpu().numpy())
 
 
-def test_fast32_statistics_match_oracle(rgs):
-    """fp32 throughput mode vs the oracle's Monte Carlo distributions on 20000 S0 games x 200 steps:
-    per-step event rates within 3 %, goal totals within 5 sigma (Poisson), identical live-step counts
-    for undecided games, and the one-step error on contact-free steps below 1e-5."""
-    n, steps, hold = 20000, 200, 10
-    pd = tl.default_params(winning_score=4)
-    x0, acts = tl.synth_inputs(2027, 0, n, 2, steps // hold)
+@pytest.mark.parametrize("n_team,dt,tau_puck,tau_player,pm,km", [
+    (2, 0.02, 0.1, 0.5, 1.0, 0.5), (2, 0.05, 0.1, 0.5, 1.0, 0.5), (2, 0.05, 1.0, 0.5, 1.0, 0.5), (2, 0.1, 0.1, 0.5, 1.0, 0.5),
+    (2, 0.2, 0.1, 0.5, 1.0, 0.5), (2, 0.2, 1.0, 0.2, 2.0, 0.1), (1, 0.1, 0.1, 0.5, 1.0, 0.5), (3, 0.1, 0.1, 0.5, 1.0, 0.5),
+    (4, 0.1, 0.1, 0.5, 1.0, 0.5), (7, 0.1, 0.1, 0.5, 1.0, 0.5)])
+def test_fast64_single_step_sweep(rgs, n_team, dt, tau_puck, tau_player, pm, km):
+    """Every state of an oracle rollout stepped ONCE by the oracle and by K2 (fp64) on the GPU, clock 0 on both sides,
+    swept over dt, tau, masses and team size (round-1 advisor finding: K2 departed on ordinary wall contacts as dt
+    grew).  Bar: event-hash mismatch rate < 1e-3, no hash-identical step with a state error, identical event records
+    (incl. the number of correctOverlap fixes) on the hash-identical steps."""
+    n, steps, hold = (300, 40, 10) if n_team <= 2 else (100, 40, 10)
+    pd = tl.default_params(n_team=n_team, winning_score=1 << 30, dt=dt, tau_puck=tau_puck, tau_player=tau_player,
+                           player_mass=pm, puck_mass=km)
+    x0, acts = tl.synth_inputs(42, 0, n, n_team, steps // hold)
+    s0 = tl.oracle_reset(pd, x0)
+    o = tl.oracle_rollout(pd, s0, acts, steps, hold, traj=True)
+    before = np.ascontiguousarray(np.concatenate([s0[:, None], o["traj"][:, :-1]], axis=1).reshape(n * steps, -1))
+    a1 = np.ascontiguousarray(np.repeat(acts, hold, axis=1)[:, :steps].reshape(n * steps, 1, 2 * n_team, 2))
+    ro = tl.oracle_rollout(pd, before, a1, 1, 1)
+    rg = _gpu_single_steps(rgs, "fast64", pd, before, a1)
+    same = ro["events"][:, 14] == rg["events"][:, 14]
+    err = np.abs(ro["state"] - rg["state"]).max(1)
+    assert (~same).sum() <= 1e-3 * n * steps
+    assert not (same & (err > 1e-6)).any()
+    assert np.array_equal(ro["events"][same], rg["events"][same])
+    # fp32 on the same steps: per-type event counts within 2 % (+ 3 sigma) of the oracle's
+    rf = _gpu_single_steps(rgs, "fast", pd, before, a1)
+    eo, ef = ro["events"].sum(0).astype(float), rf["events"].sum(0).astype(float)
+    for k in ("WALL_UP", "WALL_DOWN", "WALL_RIGHT", "WALL_LEFT", "PLAYER_PLAYER", "PLAYER_PUCK"):
+        assert abs(ef[tl.EV[k]] - eo[tl.EV[k]]) <= 0.02 * eo[tl.EV[k]] + 3 * np.sqrt(eo[tl.EV[k]] + 1), (k, eo[tl.EV[k]], ef[tl.EV[k]])
+
+
+@pytest.mark.parametrize("n_team,n,steps", [(1, 4000, 100), (3, 2000, 100), (4, 2000, 100), (7, 2000, 100)])
+def test_fast_nvn_tracks_oracle(rgs, n_team, n, steps):
+    """K2 for team sizes other than the reference's 2 against the n-v-n oracle (the plain-C restatement; the
+    reference itself is 2v2 only): fp64 -- share of event-hash-identical games, integer outcomes equal on those, per-type
+    event rates on all; fp32 -- per-type event rates and goal totals."""
+    hold = 10
+    pd = tl.default_params(n_team=n_team, winning_score=3)
+    x0, acts = tl.synth_inputs(7, 0, n, n_team, steps // hold)
     o = tl.oracle_rollout(pd, tl.oracle_reset(pd, x0), acts, steps, hold)
-    _, g = _gpu_rollout(rgs, "fast", pd, x0, acts.astype(np.float32), steps, hold)
-    eo, eg = o["events"].sum(0).astype(float), g["events"].sum(0).astype(float)
-    for k in ("WALL_UP", "WALL_DOWN", "WALL_RIGHT", "WALL_LEFT"):
-        assert abs(eg[tl.EV[k]] - eo[tl.EV[k]]) / eo[tl.EV[k]] < 0.03, k
-    # body-body counts are dominated by jammed contacts, whose count in the reference depends on the
-    # rounding noise of its absolute clock (see rgs_testlib.oracle_rollout_reltime): compare those
-    # with the reference arithmetic run on a step-relative clock, and loosely with the absolute one
-    orel = tl.oracle_rollout_reltime(pd, tl.oracle_reset(pd, x0[:6000]), acts[:6000], steps, hold)
-    er, eg6 = orel["events"].sum(0).astype(float), g["events"][:6000].sum(0).astype(float)
-    for k in ("PLAYER_PLAYER", "PLAYER_PUCK"):
-        assert abs(eg6[tl.EV[k]] - er[tl.EV[k]]) / er[tl.EV[k]] < 0.04, k
-        assert abs(eg[tl.EV[k]] - eo[tl.EV[k]]) / eo[tl.EV[k]] < 0.10, k
-    assert abs(np.median(g["events"][:, 6]) - np.median(o["events"][:, 6])) <= 1
-    goals_o, goals_g = eo[0] + eo[1], eg[0] + eg[1]
-    assert abs(goals_g - goals_o) < 5 * np.sqrt(goals_o + 1)
-    assert abs((g["state"][:, 0] > g["state"][:, 1]).mean() - (o["state"][:, 0] > o["state"][:, 1]).mean()) < 0.01
-    # emulator (g++) == GPU, bit for bit, also in fp32 (explicit FMAs, -fmad=false)
-    e = tl.emu_rollout(dict(pd, mode=tl.MODE_FAST_F32), tl.oracle_reset(pd, x0[:48]), acts[:48], steps, hold)
-    assert np.array_equal(e["state"], g["state"][:48]) and np.array_equal(e["events"], g["events"][:48])
+    _, g = _gpu_rollout(rgs, "fast64", pd, x0, acts, steps, hold)
+    same = o["events"][:, 14] == g["events"][:, 14]
+    assert same.mean() >= 0.97, same.mean()
+    assert np.array_equal(o["events"][same][:, :14], g["events"][same][:, :14])
+    assert np.array_equal(o["state"][same][:, :2], g["state"][same][:, :2])
+    assert np.median(np.abs(o["state"] - g["state"])[same].max(1)) < 1e-8
+    _, f = _gpu_rollout(rgs, "fast", pd, x0, acts.astype(np.float32), steps, hold)
+    eo = o["events"].sum(0).astype(float)
+    for name, r in (("fast64", g), ("fast", f)):
+        er = r["events"].sum(0).astype(float)
+        for k in ("WALL_UP", "WALL_DOWN", "WALL_RIGHT", "WALL_LEFT", "PLAYER_PLAYER", "PLAYER_PUCK"):
+            tol = 0.02 if name == "fast64" else 0.04
+            assert abs(er[tl.EV[k]] - eo[tl.EV[k]]) <= tol * eo[tl.EV[k]] + 3 * np.sqrt(eo[tl.EV[k]] + 1), (name, k, eo[tl.EV[k]], er[tl.EV[k]])
+        goals_o, goals_r = eo[0] + eo[1], er[0] + er[1]
+        assert abs(goals_r - goals_o) < 5 * np.sqrt(goals_o + 1)
+        assert np.array_equal(o["events"][:, tl.EV["LIVE_STEPS"]] == steps, r["events"][:, tl.EV["LIVE_STEPS"]] == steps) or \
+            abs((o["events"][:, 10] == steps).mean() - (r["events"][:, 10] == steps).mean()) < 0.01
+
+
+def _chi2_two_sample(a, b):
+    """Two-sample chi-square statistic of homogeneity and its degrees of freedom (cells empty in both dropped)."""
+    a, b = np.asarray(a, float).ravel(), np.asarray(b, float).ravel()
+    keep = (a + b) > 0
+    a, b = a[keep], b[keep]
+    ka, kb = np.sqrt(b.sum() / a.sum()), np.sqrt(a.sum() / b.sum())
+    return float((((ka * a - kb * b) ** 2) / (a + b)).sum()), int(keep.sum() - 1)
+
+
+def test_fast32_score_distribution_vs_reference(rgs):
+    """North star: "an fp32 throughput mode is validated statistically against the reference's Monte Carlo score
+    distributions".  Fixture tests/golden/mc_hist_2v2.npz = the UNMODIFIED reference's 5x5 score histogram, wins and
+    event totals on 10^5 S0 games x 200 steps at winning_score 4 (tests/golden/make_mc_hist.py).
+    (a) the SAME 10^5 games on the GPU in fp32: K4's histogram cell by cell within the paired-sampling noise of the
+        games whose score differs, event totals per type within 1 %;
+    (b) 10^6 OTHER games (different seed) on the GPU: two-sample chi-square of the 5x5 histogram and of wins
+        A / B / undecided against the reference sample, p > 0.001."""
+    from scipy.stats import chi2
+
+    fx = np.load(os.path.join(os.path.dirname(__file__), "golden", "mc_hist_2v2.npz"))
+    n, steps, hold, seed, ws = int(fx["n"]), int(fx["steps"]), int(fx["hold"]), int(fx["seed"]), int(fx["winning_score"])
+    sim = rgs.BatchedGameSim(n, mode="fast", winning_score=ws)
+    x0, acts = rgs.synth_inputs(n, steps // hold, seed=seed, dtype=torch.float32)
+    sim.reset(x0_ball=x0)
+    sim.run(acts, n_steps=steps, hold=hold)
+    stats = sim.stats().cpu().numpy()
+    hist_g = stats[32:57].reshape(5, 5)
+    sc_g = sim.state()[:, :2].cpu().numpy().astype(np.int8)
+    sc_o = fx["scores"]
+    differ = int((sc_g != sc_o).any(1).sum())
+    assert differ < 0.02 * n, differ                       # measured: see DESIGN.md section 4
+    # a game whose score differs moves one count out of one cell and into another: |delta cell| <= differ, and for
+    # unbiased differences ~ sqrt(differ)
+    d = hist_g - fx["hist"]
+    assert np.abs(d).max() <= 4 * np.sqrt(differ + 1), (d, differ)
+    assert abs(int(stats[1]) - int(fx["wins"][0])) <= 4 * np.sqrt(differ + 1)
+    assert abs(int(stats[2]) - int(fx["wins"][1])) <= 4 * np.sqrt(differ + 1)
+    ev_g, ev_o = stats[8:22].astype(float), fx["events"][:14].astype(float)
+    for k in ("WALL_UP", "WALL_DOWN", "WALL_RIGHT", "WALL_LEFT", "PLAYER_PLAYER", "PLAYER_PUCK", "GOALS_A", "GOALS_B"):
+        assert abs(ev_g[tl.EV[k]] - ev_o[tl.EV[k]]) <= 0.01 * ev_o[tl.EV[k]] + 3 * np.sqrt(ev_o[tl.EV[k]]), (k, ev_o[tl.EV[k]], ev_g[tl.EV[k]])
+    # (b) independent sample
+    m = 1_000_000
+    sim2 = rgs.BatchedGameSim(m, mode="fast", winning_score=ws)
+    x0, _ = rgs.synth_inputs(m, 0, seed=seed + 77, dtype=torch.float32)
+    sim2.reset(x0_ball=x0)
+    sim2.run_synth(seed + 77, steps, hold=hold)
+    st2 = sim2.stats().cpu().numpy()
+    c2, dof = _chi2_two_sample(fx["hist"], st2[32:57].reshape(5, 5))
+    assert chi2.sf(c2, dof) > 1e-3, (c2, dof)
+    c2w, dofw = _chi2_two_sample(fx["wins"], st2[1:4])
+    assert chi2.sf(c2w, dofw) > 1e-3, (c2w, dofw)
 
 
 def test_fast32_full_size_properties(rgs):

@@ -79,22 +79,6 @@ def tick_device():
 
 sec = timed(tick_device, reps=12)
 out["sampler_tick"] = {"candidates": C, "horizon": H, "device_ms": sec * 1e3, "candidate_steps_per_s": C * H / sec}
-# games per one-warp CTA for batches below one full CTA per SM (RGS_SMALL_LANES overrides the library's choice)
-import os  # noqa: E402
-
-sweep = {}
-for lanes in (32, 16, 8, 6, 4, 3, 2, 1):
-    os.environ["RGS_SMALL_LANES"] = str(lanes)
-    sweep[str(lanes)] = timed(tick_device, reps=12) * 1e3
-os.environ.pop("RGS_SMALL_LANES")
-out["sampler_tick"]["device_ms_by_lanes_per_warp"] = sweep
-# the superseded warp-per-game kernel (lanes over body pairs) on the same tick: lower latency per game?
-os.environ["RGS_K2_WARP"] = "1"
-lane_sim, sim = sim, BatchedGameSim(C, mode="fast")
-os.environ.pop("RGS_K2_WARP")
-out["sampler_tick"]["device_ms_warp_per_game_kernel"] = timed(tick_device, reps=12) * 1e3
-sim = lane_sim
-
 import time  # noqa: E402
 
 best = None
