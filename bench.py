@@ -42,6 +42,7 @@ def parse():
     ap.add_argument("--cpu-games-per-core", type=int, default=192)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip modes / configs / latency (tools/bench_extras.py)")
     ap.add_argument("--_worker", nargs=4, default=None, help=argparse.SUPPRESS)
     return ap.parse_args()
 
@@ -77,11 +78,12 @@ def _worker(npz, lo, hi, horizon):
     dp = C.POINTER(C.c_double)
     final = np.zeros((n, 22))
     if kind == "reference":
-        lib.ref_rollout_batch.argtypes = [C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_int, dp, dp, C.c_int64,
-                                          C.c_double, C.c_double, C.c_double, C.c_double, dp]
+        lib.ref_rollout_batch_live.restype = C.c_int64
+        lib.ref_rollout_batch_live.argtypes = [C.c_int64, C.c_int64, C.c_int64, C.c_double, C.c_int, dp, dp, C.c_int64,
+                                               C.c_double, C.c_double, C.c_double, C.c_double, dp]
         t0 = time.perf_counter()
-        lib.ref_rollout_batch(n, horizon, HOLD, 0.05, WINNING_SCORE, x0.ctypes.data_as(dp), acts.ctypes.data_as(dp),
-                              n_act, 0.1, 0.5, 1.0, 0.5, final.ctypes.data_as(dp))
+        live = lib.ref_rollout_batch_live(n, horizon, HOLD, 0.05, WINNING_SCORE, x0.ctypes.data_as(dp),
+                                          acts.ctypes.data_as(dp), n_act, 0.1, 0.5, 1.0, 0.5, final.ctypes.data_as(dp))
         sec = time.perf_counter() - t0
     else:
         sys.path.insert(0, os.path.join(ROOT, "tests"))
@@ -90,10 +92,12 @@ def _worker(npz, lo, hi, horizon):
         pd = tl.default_params(winning_score=WINNING_SCORE)
         s0 = tl.oracle_reset(pd, x0)
         t0 = time.perf_counter()
-        final = tl.oracle_rollout(pd, s0, acts, horizon, HOLD, threads=1)["state"]
+        r = tl.oracle_rollout(pd, s0, acts, horizon, HOLD, threads=1)
         sec = time.perf_counter() - t0
+        final, live = r["state"], int(r["events"][:, tl.EV["LIVE_STEPS"]].sum())
     decided = int(((final[:, 0] >= WINNING_SCORE) | (final[:, 1] >= WINNING_SCORE)).sum())
-    print(json.dumps({"steps": n * horizon, "seconds": sec, "decided": decided}))
+    # LIVE game-steps (run() is a no-op once a game is decided), the same basis as the GPU arm's value
+    print(json.dumps({"steps": int(live), "seconds": sec, "decided": decided}))
 
 
 def cpu_pass(x0, acts, horizon, cores):
@@ -141,6 +145,7 @@ def run_reference_arm(args):
         steps += s
         sec += t
     value = steps / sec
+    games_timed = int(x0.shape[0]) * args.steps
     sample = f"{x0.shape[0]} games x {args.horizon} steps per pass ({cores} processes x {args.cpu_games_per_core} games), first games of the S0 workload"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": "game-steps/s", "n_gpus": args.gpus,
@@ -148,6 +153,7 @@ def run_reference_arm(args):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": workload_config(args, args.gpus),
         "cpu_baseline": {"value": value, "unit": "game-steps/s", "cores": cores, "kind": kind, "sample": sample},
+        "games_timed": games_timed, "live_game_steps_timed": int(steps),
         "e2e": {"value": value, "unit": "game-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
@@ -347,15 +353,19 @@ def main():
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     esz = 4 if args.mode == "fast" else 8
     alg_bytes = G * (2 * 22 * 8 + 2 * 16 * 8 + 8) + G * n_act * 8 * esz   # state+events in/out, clock, commands
-    traffic = None
+    # DRAM traffic is measured nowhere but in ncu (--set full capture of the rollout kernel); the file names the
+    # commit the capture was taken on, so a stale figure is visible in the line
+    traffic, traffic_src = None, None
     tfile = os.path.join(ROOT, "profiles", "traffic_latest.json")
-    if os.path.exists(tfile):
+    if os.path.exists(tfile) and args.mode == "fast":
         try:
-            traffic = json.load(open(tfile)).get("dram_bytes_per_launch")
+            tj = json.load(open(tfile))
+            traffic = tj.get("dram_bytes_per_launch")
+            traffic_src = {k: tj.get(k) for k in ("source", "commit", "kernel")}
         except (OSError, ValueError):
             pass
     roofline = {"bound": "fp64-issue" if fp64_mode else "fp32-issue", "achieved": achieved, "peak": pk.value,
-                "unit": "TFLOP/s", "frac": achieved / pk.value if pk.value else None, "traffic": traffic,
+                "unit": "TFLOP/s", "frac": achieved / pk.value if pk.value else None, "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": "rgs_measure_peak FMA micro-kernel on this GPU (MEASURED_PEAKS.json holds only HBM and bf16 tensor peaks; "
                                "this path uses neither)",
                 "flop_per_game_step": W, "kernel_ms": kernel_ms, "game_steps_per_launch": live_per_gpu_launch,
@@ -375,6 +385,15 @@ def main():
                         "sample": f"{cx0.shape[0]} games x {H} steps ({cores} processes x {args.cpu_games_per_core} games), "
                                   f"first games of the same S0 workload, fp64 C++ GameSim at -O2"}
 
+    extras = {}
+    if world == 1 and not args.no_extras:
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        from bench_extras import measure_extras
+
+        del sim, x0, acts
+        torch.cuda.empty_cache()
+        extras = measure_extras(local_rank, hbm_peak)
+
     line = {"metric": METRIC, "value": value, "unit": "game-steps/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / max(1, args.steps), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": {"fast": "f32", "exact": "f64", "fast64": "f64"}[args.mode],
@@ -382,6 +401,11 @@ def main():
             "gpu_launches": int(launches), "roofline": roofline, "cpu_baseline": cpu_baseline,
             "stats": {"live_game_steps_per_pass": live_per_pass, "games": int(st[0]), "goals": int(st[8] + st[9]),
                       "events_per_step": float(st[10:16].sum()) / max(1, live_per_pass)}}
+    if cpu_baseline:
+        line["vs_cpu_baseline"] = {"device_timed": value / cpu_baseline["value"],
+                                   "e2e": (e2e["value"] / cpu_baseline["value"]) if e2e else None,
+                                   "cores": cpu_baseline["cores"], "basis": "live game-steps on both arms"}
+    line.update(extras)
     emit(line)
     if world > 1:
         dist.destroy_process_group()

@@ -94,10 +94,23 @@ void ref_rollout(void *h, const double *actions, int64_t n_steps, double *out_st
 // PROCESS per core is the only safe parallelism).
 //   x0_ball : [n_games,4]; actions: [n_games, n_act, 8] where action index = step / hold
 //   out_final : [n_games,22]
+int64_t ref_rollout_batch_live(int64_t n_games, int64_t n_steps, int64_t hold, double dt, int winning_score,
+                               const double *x0_ball, const double *actions, int64_t n_act, double tau_puck,
+                               double tau_player, double player_mass, double puck_mass, double *out_final);
 void ref_rollout_batch(int64_t n_games, int64_t n_steps, int64_t hold, double dt, int winning_score,
                        const double *x0_ball, const double *actions, int64_t n_act, double tau_puck,
                        double tau_player, double player_mass, double puck_mass, double *out_final) {
+    ref_rollout_batch_live(n_games, n_steps, hold, dt, winning_score, x0_ball, actions, n_act, tau_puck, tau_player,
+                           player_mass, puck_mass, out_final);
+}
+
+// Same, and returns the number of LIVE steps: run() calls made while undecided() (GameSim::run is a no-op once a
+// game is decided, src/GameSim.cpp:121-123), the basis the GPU arm's game-steps/s is counted on.
+int64_t ref_rollout_batch_live(int64_t n_games, int64_t n_steps, int64_t hold, double dt, int winning_score,
+                               const double *x0_ball, const double *actions, int64_t n_act, double tau_puck,
+                               double tau_player, double player_mass, double puck_mass, double *out_final) {
     GameSim g;
+    int64_t live = 0;
     for (int64_t n = 0; n < n_games; ++n) {
         const double *x0 = x0_ball + 4 * n;
         g.reset(dt, winning_score, Eigen::Vector4d(x0[0], x0[1], x0[2], x0[3]), 0.0, false, std::string(""),
@@ -105,10 +118,12 @@ void ref_rollout_batch(int64_t n_games, int64_t n_steps, int64_t hold, double dt
         Eigen::Matrix<double, SimState::SIZE, 1> s = g.state_.vector();
         for (int64_t k = 0; k < n_steps; ++k) {
             const double *a = actions + 8 * (n * n_act + k / hold);
+            live += g.undecided() ? 1 : 0;
             s = g.run(v2(a), v2(a + 2), v2(a + 4), v2(a + 6));
         }
         if (out_final) copy_state(s, out_final + 22 * n);
     }
+    return live;
 }
 
 }  // extern "C"

@@ -47,6 +47,19 @@ def main():
                                   out.ctypes.data_as(dp))
             assert np.array_equal(out, o["state"][:REF_SAMPLE]), "restatement != compiled reference"
         print(f"{g0 + chunk} games, {time.time() - t0:.0f} s", flush=True)
+    # second pass, winning_score = 1: S0 games rarely see two goals in 200 steps, so the win / undecided split and the
+    # time to the first goal are the informative part of the score distribution
+    pd1 = tl.default_params(winning_score=1)
+    wins1 = np.zeros(3, dtype=np.int64)
+    decided_hist = np.zeros(STEPS // 20 + 1, dtype=np.int64)   # [k] = games decided in steps (20 k, 20 k + 20]; last = never
+    for g0 in range(0, N, chunk):
+        x0, acts = tl.synth_inputs(SEED, g0, chunk, 2, STEPS // HOLD)
+        o = tl.oracle_rollout(pd1, tl.oracle_reset(pd1, x0), acts, STEPS, HOLD, threads=8)
+        a, b = o["state"][:, 0] >= 1, o["state"][:, 1] >= 1
+        wins1 += np.array([a.sum(), (b & ~a).sum(), (~a & ~b).sum()])
+        ds = o["events"][:, tl.EV["DECIDED_STEP"]]
+        np.add.at(decided_hist, np.where(ds > 0, (ds - 1) // 20, STEPS // 20), 1)
+        print(f"ws=1: {g0 + chunk} games, {time.time() - t0:.0f} s", flush=True)
     hist = np.zeros((5, 5), dtype=np.int64)
     np.add.at(hist, (np.minimum(scores[:, 0], 4), np.minimum(scores[:, 1], 4)), 1)
     wins_a = int((scores[:, 0] >= WS).sum())
@@ -56,7 +69,9 @@ def main():
     np.savez_compressed(os.path.join(HERE, "mc_hist_2v2.npz"), n=N, steps=STEPS, hold=HOLD, seed=SEED, winning_score=WS,
                         hist=hist, wins=np.array([wins_a, wins_b, N - wins_a - wins_b]), events=ev, event_names=ev_names,
                         scores=scores, a_leads=int((scores[:, 0] > scores[:, 1]).sum()),
-                        b_leads=int((scores[:, 1] > scores[:, 0]).sum()), ref_sample_checked=REF_SAMPLE)
+                        b_leads=int((scores[:, 1] > scores[:, 0]).sum()), ref_sample_checked=REF_SAMPLE,
+                        wins_ws1=wins1, decided_hist_ws1=decided_hist)
+    print("wins ws=1", wins1, "decided hist", decided_hist)
     print("hist\n", hist, "\nwins", wins_a, wins_b, "events", dict(zip(ev_names.tolist(), ev.tolist())))
 
 

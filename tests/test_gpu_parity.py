@@ -335,7 +335,8 @@ def test_fast32_score_distribution_vs_reference(rgs):
     ev_g, ev_o = stats[8:22].astype(float), fx["events"][:14].astype(float)
     for k in ("WALL_UP", "WALL_DOWN", "WALL_RIGHT", "WALL_LEFT", "PLAYER_PLAYER", "PLAYER_PUCK", "GOALS_A", "GOALS_B"):
         assert abs(ev_g[tl.EV[k]] - ev_o[tl.EV[k]]) <= 0.01 * ev_o[tl.EV[k]] + 3 * np.sqrt(ev_o[tl.EV[k]]), (k, ev_o[tl.EV[k]], ev_g[tl.EV[k]])
-    # (b) independent sample
+    # (b) independent sample, winning_score 4 (the 5x5 histogram) and 1 (wins A / B / undecided, time to the first goal:
+    # S0 games rarely see two goals in 200 steps, so the decided split only exists at winning_score 1)
     m = 1_000_000
     sim2 = rgs.BatchedGameSim(m, mode="fast", winning_score=ws)
     x0, _ = rgs.synth_inputs(m, 0, seed=seed + 77, dtype=torch.float32)
@@ -343,9 +344,17 @@ def test_fast32_score_distribution_vs_reference(rgs):
     sim2.run_synth(seed + 77, steps, hold=hold)
     st2 = sim2.stats().cpu().numpy()
     c2, dof = _chi2_two_sample(fx["hist"], st2[32:57].reshape(5, 5))
-    assert chi2.sf(c2, dof) > 1e-3, (c2, dof)
-    c2w, dofw = _chi2_two_sample(fx["wins"], st2[1:4])
-    assert chi2.sf(c2w, dofw) > 1e-3, (c2w, dofw)
+    assert dof >= 3 and chi2.sf(c2, dof) > 1e-3, (c2, dof)
+    sim3 = rgs.BatchedGameSim(m, mode="fast", winning_score=1)
+    sim3.reset(x0_ball=x0)
+    sim3.run_synth(seed + 77, steps, hold=hold)
+    st3 = sim3.stats().cpu().numpy()
+    c2w, dofw = _chi2_two_sample(fx["wins_ws1"], st3[1:4])
+    assert dofw == 2 and chi2.sf(c2w, dofw) > 1e-3, (c2w, dofw, fx["wins_ws1"], st3[1:4])
+    ds = sim3.events()[:, tl.EV["DECIDED_STEP"]].cpu().numpy()
+    dh = np.bincount(np.where(ds > 0, (ds - 1) // 20, steps // 20), minlength=steps // 20 + 1)
+    c2d, dofd = _chi2_two_sample(fx["decided_hist_ws1"], dh)
+    assert chi2.sf(c2d, dofd) > 1e-3, (c2d, dofd)
 
 
 def test_fast32_full_size_properties(rgs):
