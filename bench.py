@@ -3,7 +3,7 @@
 
 One bench "step" = one Monte Carlo pass over the per-GPU batch: batched GameSim::reset, then
 `horizon` fused game-steps of every game from device-resident fp32 command tensors (K2), then the K4
-statistics reduction (+ one NCCL all-reduce of int64[64] when N > 1).  Workload = BASELINE.json
+statistics reduction (+ one NCCL all-reduce of int64[96] when N > 1).  Workload = BASELINE.json
 configs[1] (MonteCarlo 2v2, 10^6 randomized games x 200 steps, S0 inputs); per-GPU work is fixed as
 N grows (weak scaling).  `value` counts LIVE game-steps (GameSim::run is a no-op once decided).
 
@@ -163,7 +163,7 @@ def workload_config(args, n_gpus):
                         f"game-steps, S0 inputs (puck ~U, commands ~U(-10,10) redrawn every {HOLD} steps), dt=0.05, "
                         f"winning_score={WINNING_SCORE}",
             "games_per_gpu": args.games, "horizon": args.horizon, "hold": HOLD, "players_per_team": 2,
-            "mode": args.mode, "parallelism": f"games sharded over {n_gpus} GPU(s), one all-reduce of int64[64] stats",
+            "mode": args.mode, "parallelism": f"games sharded over {n_gpus} GPU(s), one all-reduce of int64[96] stats",
             "l2": "inputs larger than L2 (fp32 command tensor 32 B x games x horizon/hold; state 176 B x games)"}
 
 
@@ -327,7 +327,7 @@ def main():
         esz = 4 if sim.action_dtype == torch.float32 else 8
         e2e = {"value": float(live.item()) * reps / float(sec.item()), "unit": "game-steps/s",
                "h2d_bytes_per_step": world * (G * 4 * 8 + G * n_act * 8 * esz),
-               "d2h_bytes_per_step": world * (G * 22 * 8 + G * 16 * 8 + 64 * 8), "passes": reps,
+               "d2h_bytes_per_step": world * (G * 22 * 8 + G * 16 * 8 + 96 * 8), "passes": reps,
                "api": "BatchedGameSim.run_host -> rgs_batch_run_host (pinned host buffers, 8 game-range chunks "
                       "double-buffered over 2 streams)"}
 

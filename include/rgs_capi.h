@@ -34,7 +34,7 @@ extern "C" {
 #define RGS_COUNTER_LIM 50 /* COLLISION_COUNTER_LIM, reference include/GameSim.h:7 */
 #define RGS_MAX_TEAM 7
 #define RGS_N_EVENTS 16
-#define RGS_N_STATS 64
+#define RGS_N_STATS 96
 
 enum { RGS_OK = 0, RGS_EINVAL = -1, RGS_ECUDA = -2, RGS_ENOMEM = -3, RGS_EUNSUPPORTED = -4 };
 
@@ -60,7 +60,13 @@ enum {
     RGS_ST_LEAD_A = 4, RGS_ST_LEAD_B = 5, RGS_ST_TIED = 6, /* by score at the end, decided or not */
     RGS_ST_EVENTS0 = 8,      /* + RGS_EV_*: sums of the first 14 event fields (not the hash) */
     RGS_ST_SCORE_HIST = 32,  /* + 5*min(TAS,4) + min(TBS,4): 25-bin joint score histogram */
+    /* damage (reference src/GameSim.cpp:277-282, SimState.h:33-38; read back per run by
+     * matlab/interpret_mc_results.m:37-48), summed over the games in fixed point: units of 1/RGS_DAMAGE_FIXED_SCALE */
+    RGS_ST_DAMAGE = 64,      /* + 4*aggressor + victim (A1,A2,B1,B2 = 0..3): 2v2 batches only, else 0 */
+    RGS_ST_DAMAGE_TEAM = 80, /* + 2*(aggressor in team B) + (victim in team B): any team size */
+    RGS_ST_OVERLAP_FIXES = 84 /* sum of RGS_EV_OVERLAP_FIXES */
 };
+#define RGS_DAMAGE_FIXED_SCALE 16777216 /* 2^24 */
 
 /* Constructor constants (reference src/GameSim.cpp:5-9) and reset() arguments (:21-25). */
 typedef struct rgs_params {
@@ -173,6 +179,22 @@ int rgs_synth_inputs(int device, uint64_t seed, int64_t first_game, int64_t n, i
 /* Roofline denominator measured on the spot: dependent-FMA-chain micro-kernel on every SM, fp32
  * (fp64 = 0) or fp64 (fp64 = 1); result in FMA TFLOP/s (2 flop per FMA).  Synchronous. */
 int rgs_measure_peak(int device, int32_t fp64, double *out_tflops);
+
+/* Batched log writer: one binary log file per game in the reference's record format (replaces Logger::log /
+ * logVectors, reference include/utils.h:66-76, as driven by src/GameSim.cpp:161-170 with log = true; read back by
+ * matlab/interpret_mc_results.m:29-50 and matlab/visualize_mc_game.m).  Host-side I/O only, no device work.
+ *   h_traj       [n_games, n_rec, 1 + (2+4E) + (2n)^2] doubles in HOST memory: the trajectory tensor of
+ *                rgs_batch_run / _run_synth / _run_policy with log_stride = 1, copied to the host
+ *   h_n_records  [n_games] records to write per game, or NULL = n_rec (the reference stops logging once a game is
+ *                decided, src/GameSim.cpp:121-123: pass the LIVE_STEPS of the launch)
+ *   path_pattern file name with one "{}" that is replaced by first_index + g (py/MonteCarlo.py:26: mc_run_{i}.log)
+ *   layout       0 = reference: record = t, TAS, TBS, puck x y, players x y, then the damage fields exactly as the
+ *                reference writes them (damage.row(k) logged as 2n CONTIGUOUS doubles from &damage(k,0) of a
+ *                column-major matrix, utils.h:75) -> byte-identical files; 1 = row_major: true rows damage(k, :)
+ *   append       0 truncates the files, 1 appends (the priming step and the main run are two launches) */
+int rgs_write_logs(const double *h_traj, int64_t n_games, int64_t n_rec, int32_t players_per_team,
+                   const int64_t *h_n_records, const char *path_pattern, int64_t first_index, int32_t layout,
+                   int32_t append);
 
 /* Host-buffer entry point (the call MonteCarlo-style callers make; bench.py's e2e): copies
  * h_x0_ball [n_games,4] doubles and h_actions [n_games,n_act,4n] (compute type) to the device in

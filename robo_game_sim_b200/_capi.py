@@ -11,13 +11,14 @@ LIB_PATH = os.environ.get("RGS_B200_LIB") or os.path.join(_HERE, "librgs_b200.so
 
 RGS_OK, RGS_EINVAL, RGS_ECUDA, RGS_ENOMEM, RGS_EUNSUPPORTED = 0, -1, -2, -3, -4
 MODE_EXACT_F64, MODE_FAST_F32, MODE_FAST_F64 = 64, 32, 65
-N_EVENTS, N_STATS, MAX_TEAM = 16, 64, 7
+N_EVENTS, N_STATS, MAX_TEAM = 16, 96, 7
 
 EV_NAMES = ["goals_a", "goals_b", "wall_up", "wall_down", "wall_right", "wall_left", "player_player", "player_puck",
             "discarded", "loop_iters", "live_steps", "decided_step", "counter_limit", "base_clamp", "hash",
             "overlap_fixes"]
 ST_GAMES, ST_WINS_A, ST_WINS_B, ST_UNDECIDED, ST_LEAD_A, ST_LEAD_B, ST_TIED = range(7)
 ST_EVENTS0, ST_SCORE_HIST = 8, 32
+ST_DAMAGE, ST_DAMAGE_TEAM, ST_OVERLAP_FIXES, DAMAGE_FIXED_SCALE = 64, 80, 84, float(1 << 24)
 
 
 class RgsParams(C.Structure):
@@ -57,6 +58,7 @@ SIGNATURES = {
     "rgs_batch_terminal_cost": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "rgs_synth_inputs": (C.c_int, [C.c_int, _u64, _i64, _i64, _i32, _i64, _dbl, _vp, _vp, _i32, _vp]),
     "rgs_measure_peak": (C.c_int, [C.c_int, _i32, C.POINTER(_dbl)]),
+    "rgs_write_logs": (C.c_int, [_vp, _i64, _i64, _i32, _vp, C.c_char_p, _i64, _i32, _i32]),
     "rgs_batch_run_host": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
     "rgs_single_create": (C.c_int, [C.POINTER(_vp), C.c_int]),
     "rgs_single_destroy": (C.c_int, [_vp]),

@@ -195,9 +195,12 @@ cudaError_t launch_synth(uint64_t seed, int64_t first_game, int64_t n, int n_tea
 }
 
 // ---- K4: statistics ------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) stats_kernel(int64_t n_games, int srec, const double *__restrict__ state,
-                                                    const long long *__restrict__ events, int winning_score,
-                                                    unsigned long long *__restrict__ stats) {
+// Damage (reference src/GameSim.cpp:277-282; histogrammed per run by matlab/interpret_mc_results.m:37-48) is summed
+// in FIXED POINT (RGS_DAMAGE_FIXED_SCALE units, rounded per game) so that the whole vector stays one integer
+// all-reduce and the sum does not depend on the order of the games.
+__global__ void __launch_bounds__(256) stats_kernel(int64_t n_games, int srec, int np, const double *__restrict__ state,
+                                                    const long long *__restrict__ events, const double *__restrict__ damage,
+                                                    int winning_score, unsigned long long *__restrict__ stats) {
     __shared__ unsigned long long sh[RGS_N_STATS];
     if (threadIdx.x < RGS_N_STATS) sh[threadIdx.x] = 0ull;
     __syncthreads();
@@ -225,6 +228,20 @@ __global__ void __launch_bounds__(256) stats_kernel(int64_t n_games, int srec, c
             acc[2 * k] += e.x;
             acc[2 * k + 1] += e.y;
         }
+        if (ev[7].y != 0) atomicAdd(&sh[RGS_ST_OVERLAP_FIXES], (unsigned long long)ev[7].y);
+        if (ev[3].x != 0) {  // only games with player-player impacts carry damage
+            const double *dm = damage + g * (np * np);
+            const int nt = np >> 1;
+            for (int a = 0; a < np; ++a)
+                for (int v = 0; v < np; ++v) {
+                    const double d = dm[a * np + v];
+                    if (d != 0.0) {
+                        const unsigned long long q = (unsigned long long)llrint(d * (double)RGS_DAMAGE_FIXED_SCALE);
+                        atomicAdd(&sh[RGS_ST_DAMAGE_TEAM + 2 * (a >= nt) + (v >= nt)], q);
+                        if (np == 4) atomicAdd(&sh[RGS_ST_DAMAGE + 4 * a + v], q);
+                    }
+                }
+        }
     }
 #pragma unroll
     for (int k = 0; k < 14; ++k) {
@@ -236,15 +253,15 @@ __global__ void __launch_bounds__(256) stats_kernel(int64_t n_games, int srec, c
     if (threadIdx.x < RGS_N_STATS && sh[threadIdx.x] != 0ull) atomicAdd(&stats[threadIdx.x], sh[threadIdx.x]);
 }
 
-cudaError_t launch_stats(int n_team, int64_t n_games, const double *state, const long long *events, int winning_score,
-                         long long *d_stats, cudaStream_t stream, int sm_count) {
+cudaError_t launch_stats(int n_team, int64_t n_games, const double *state, const long long *events, const double *damage,
+                         int winning_score, long long *d_stats, cudaStream_t stream, int sm_count) {
     cudaError_t err = cudaMemsetAsync(d_stats, 0, sizeof(long long) * RGS_N_STATS, stream);
     if (err != cudaSuccess) return err;
     const int threads = 256;
     int64_t blocks = (n_games + threads - 1) / threads;
     if (blocks > (int64_t)sm_count * 4) blocks = (int64_t)sm_count * 4;
     if (blocks < 1) blocks = 1;
-    stats_kernel<<<(unsigned)blocks, threads, 0, stream>>>(n_games, 2 + 4 * (2 * n_team + 1), state, events,
+    stats_kernel<<<(unsigned)blocks, threads, 0, stream>>>(n_games, 2 + 4 * (2 * n_team + 1), 2 * n_team, state, events, damage,
                                                            winning_score, reinterpret_cast<unsigned long long *>(d_stats));
     return cudaGetLastError();
 }

@@ -393,7 +393,7 @@ int rgs_batch_stats(rgs_batch *b, int64_t *d_stats, void *stream) {
     if (!d_stats) return fail(RGS_EINVAL, "d_stats is NULL");
     DeviceGuard guard(b->device);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    cudaError_t e = rgs::launch_stats(b->n_team, b->n_games, b->state, b->events, b->p.winning_score, b->stats, s, b->sm_count);
+    cudaError_t e = rgs::launch_stats(b->n_team, b->n_games, b->state, b->events, b->damage, b->p.winning_score, b->stats, s, b->sm_count);
     if (e != cudaSuccess) return cuda_fail(e, "stats kernel launch");
     g_launches.fetch_add(1);
     RGS_CUDA(cudaMemcpyAsync(d_stats, b->stats, RGS_N_STATS * sizeof(long long), cudaMemcpyDefault, s));
@@ -489,6 +489,63 @@ int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_acti
     }
     RGS_CUDA(cudaStreamSynchronize(b->streams[1]));
     RGS_CUDA(cudaStreamSynchronize(b->streams[0]));
+    return RGS_OK;
+}
+
+// One binary log per game in the reference's on-disk format (src/GameSim.cpp:161-170, include/utils.h:66-76): per
+// record t, TAS, TBS, puck x y, every player's x y, then (2n)^2 damage fields (29 doubles at 2v2).
+// layout 0 ("reference"): damage.row(k) is logged by utils.h:75 as 2n CONTIGUOUS doubles from &damage(k,0) of a
+// COLUMN-major matrix, i.e. linear indices k .. k+2n-1 of the column-major buffer -- not a row; kept so that files
+// are byte-identical to the reference's.  layout 1 ("row_major"): the true rows, damage(aggressor, victim), which is
+// what matlab/interpret_mc_results.m:37-48 assumes when it names the fields.
+int rgs_write_logs(const double *h_traj, int64_t n_games, int64_t n_rec, int32_t players_per_team, const int64_t *h_n_records,
+                   const char *path_pattern, int64_t first_index, int32_t layout, int32_t append) {
+    if (n_games < 0 || n_rec < 0) return fail(RGS_EINVAL, "n_games and n_rec must be >= 0");
+    if (n_games > 0 && n_rec > 0 && !h_traj) return fail(RGS_EINVAL, "h_traj is NULL");
+    if (players_per_team < 1 || players_per_team > RGS_MAX_TEAM) return fail(RGS_EINVAL, "players_per_team out of range");
+    if (layout != 0 && layout != 1) return fail(RGS_EINVAL, "layout must be 0 (reference) or 1 (row_major)");
+    if (!path_pattern) return fail(RGS_EINVAL, "path_pattern is NULL");
+    const std::string pat(path_pattern);
+    const size_t brace = pat.find("{}");
+    if (brace == std::string::npos || pat.find("{}", brace + 2) != std::string::npos)
+        return fail(RGS_EINVAL, "path_pattern must contain exactly one {} (replaced by the run index)");
+    const int np = 2 * players_per_team, E = np + 1, srec = 2 + 4 * E, trec = 1 + srec + np * np;
+    const int frec = 3 + 2 * E + np * np;
+    std::vector<double> buf;
+    for (int64_t g = 0; g < n_games; ++g) {
+        int64_t nr = h_n_records ? h_n_records[g] : n_rec;
+        if (nr < 0) nr = 0;
+        if (nr > n_rec) nr = n_rec;
+        buf.resize((size_t)nr * frec);
+        for (int64_t r = 0; r < nr; ++r) {
+            const double *in = h_traj + ((size_t)g * n_rec + r) * trec;
+            double *out = buf.data() + (size_t)r * frec;
+            out[0] = in[0];
+            out[1] = in[1];
+            out[2] = in[2];
+            for (int e = 0; e < E; ++e) {  // positions only: velocities are not logged
+                out[3 + 2 * e] = in[3 + 4 * e];
+                out[4 + 2 * e] = in[4 + 4 * e];
+            }
+            const double *dm = in + 1 + srec;  // (aggressor, victim) row-major
+            double *od = out + 3 + 2 * E;
+            for (int k = 0; k < np; ++k)
+                for (int c = 0; c < np; ++c) {
+                    if (layout == 1) {
+                        od[k * np + c] = dm[k * np + c];
+                    } else {
+                        const int lin = k + c, row = lin % np, col = lin / np;
+                        od[k * np + c] = dm[row * np + col];
+                    }
+                }
+        }
+        const std::string path = pat.substr(0, brace) + std::to_string((long long)(first_index + g)) + pat.substr(brace + 2);
+        FILE *f = fopen(path.c_str(), append ? "ab" : "wb");
+        if (!f) return fail(RGS_EINVAL, "cannot open %s for writing", path.c_str());
+        const size_t wrote = buf.empty() ? 0 : fwrite(buf.data(), sizeof(double), buf.size(), f);
+        fclose(f);
+        if (wrote != buf.size()) return fail(RGS_EINVAL, "short write to %s", path.c_str());
+    }
     return RGS_OK;
 }
 

@@ -18,8 +18,8 @@ cudaError_t launch_rollout_lane_f64(int n_team, const rgs_params &p, const RunAr
 cudaError_t lane_scratch_bytes(int n_team, int fp64, int sm_count, size_t *bytes);
 
 // K4: per-batch statistics vector int64[RGS_N_STATS] (rgs_aux_kernels.cu)
-cudaError_t launch_stats(int n_team, int64_t n_games, const double *state, const long long *events, int winning_score,
-                         long long *d_stats, cudaStream_t stream, int sm_count);
+cudaError_t launch_stats(int n_team, int64_t n_games, const double *state, const long long *events, const double *damage,
+                         int winning_score, long long *d_stats, cudaStream_t stream, int sm_count);
 
 // K5: batched reset + synthetic S0 inputs (rgs_aux_kernels.cu)
 cudaError_t launch_reset(int n_team, int64_t n_games, const rgs_params &p, const double *d_x0_ball, int64_t x0_stride,

@@ -12,6 +12,7 @@ exists for API compatibility.
 per fused launch from device-resident action tensors (torch is used for tensor hand-off only).
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -271,7 +272,7 @@ class BatchedGameSim:
         return (s[:, 0] < w) & (s[:, 1] < w)
 
     def stats(self):
-        """K4: int64[64] statistics vector on the device (sum it across GPUs with one all-reduce)."""
+        """K4: int64[96] statistics vector on the device (sum it across GPUs with one all-reduce)."""
         torch = self._torch
         out = torch.empty(_capi.N_STATS, dtype=torch.int64, device=self.device)
         _capi.check(self._lib.rgs_batch_stats(self._h, out.data_ptr(), self._stream()))
@@ -305,11 +306,42 @@ class BatchedGameSim:
         b = best.cpu()
         return cost, int(b[0]), float(b[1:2].view(torch.float64)[0])
 
+    # ---- the reference's binary logs for a whole batch ----
+    def write_logs(self, traj, path_pattern, first_index=1, layout="reference", n_records=None, append=False):
+        """One binary log per game in the reference's record format (src/GameSim.cpp:161-170, include/utils.h:66-76;
+        29 doubles per record at 2v2), from the trajectory tensor a run with log_stride=1 returned.
+
+        path_pattern: file name with one "{}" for the run index first_index + g (py/MonteCarlo.py:26 writes
+                      mc_run_{i}.log with i from 1).
+        layout:       "reference" reproduces the reference's damage fields byte for byte (damage.row(k) logged as 4
+                      contiguous doubles of the column-major matrix); "row_major" writes the true rows
+                      damage(aggressor, :) that matlab/interpret_mc_results.m:37-48 assumes.
+        n_records:    [N] records per game (default: all); the reference stops logging once a game is decided, so
+                      pass the games' live steps of that launch to get files of the reference's length.
+        """
+        torch = self._torch
+        layouts = {"reference": 0, "row_major": 1}
+        if layout not in layouts:
+            raise ValueError("layout must be 'reference' or 'row_major'")
+        np2 = 2 * self.n_team
+        t = traj.detach().to("cpu", torch.float64).contiguous() if isinstance(traj, torch.Tensor) else \
+            torch.from_numpy(np.ascontiguousarray(traj, dtype=np.float64))
+        if t.dim() != 3 or t.shape[0] != self.n_games or t.shape[2] != 1 + self.state_size + np2 * np2:
+            raise ValueError(f"traj must have shape ({self.n_games}, records, {1 + self.state_size + np2 * np2}), got {tuple(t.shape)}")
+        nr_ptr, nr = None, None
+        if n_records is not None:
+            nr = torch.as_tensor(n_records).detach().to("cpu", torch.int64).contiguous()
+            if nr.numel() != self.n_games:
+                raise ValueError(f"n_records must have {self.n_games} elements")
+            nr_ptr = nr.data_ptr()
+        _capi.check(self._lib.rgs_write_logs(t.data_ptr(), self.n_games, int(t.shape[1]), self.n_team, nr_ptr,
+                                             os.fsencode(path_pattern), int(first_index), layouts[layout], 1 if append else 0))
+
     # ---- host-buffer entry point (end-to-end path) ----
     def run_host(self, x0_ball, actions, n_steps, hold=1, want_state=True, want_events=True, out=None):
         """x0_ball [N,4] float64 and actions [N,n_act,2n,2] (float32 in "fast" mode, else float64)
         in HOST memory (numpy or CPU torch tensors, ideally pinned).  Resets the batch, runs n_steps
-        and returns (state [N,S] f64, events [N,16] i64, stats [64] i64) as numpy arrays."""
+        and returns (state [N,S] f64, events [N,16] i64, stats [96] i64) as numpy arrays."""
         torch = self._torch
 
         def host(x, dtype):

@@ -138,7 +138,7 @@ def test_stats_naming():
     from robo_game_sim_b200 import _capi
     from robo_game_sim_b200.montecarlo import stats_to_dict
 
-    s = np.zeros(64, dtype=np.int64)
+    s = np.zeros(96, dtype=np.int64)
     s[0], s[1], s[2], s[3] = 10, 3, 2, 5
     s[_capi.ST_EVENTS0 + 10] = 2000
     s[_capi.ST_SCORE_HIST + 5 * 1 + 2] = 7
@@ -170,7 +170,7 @@ rank, world = int(sys.argv[1]), int(sys.argv[2])
 os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=sys.argv[3])
 dist.init_process_group("gloo", rank=rank, world_size=world)
 first, count = shard_range(1001, rank, world)
-stats = torch.zeros(64, dtype=torch.int64)
+stats = torch.zeros(96, dtype=torch.int64)
 stats[0] = count                       # games
 stats[1] = sum(1 for g in range(first, first + count) if g % 3 == 0)
 out = reduce_stats(stats)
@@ -181,7 +181,7 @@ print("ok")
 
 
 def test_stats_reduction_world_size_2_gloo(tmp_path):
-    """The multi-rank path: each rank owns a slice of runs, one all-reduce(sum) of int64[64]."""
+    """The multi-rank path: each rank owns a slice of runs, one all-reduce(sum) of int64[96]."""
     script = tmp_path / "w.py"
     script.write_text(_GLOO_WORKER.format(root=ROOT))
     port = str(29500 + os.getpid() % 2000)

@@ -418,6 +418,141 @@ def test_monte_carlo_batched_harness(rgs, tmp_path):
     assert out3["games"] == 64 and out3["live_steps"] == 64 * 21
 
 
+def _reference_logs(tmp_path, x0, full_actions, ws=3):
+    """mc_run-style binary logs written by the compiled reference itself, one game per file -> list of bytes."""
+    lib = tl.ref_lib()
+    dp = C.POINTER(C.c_double)
+    out = []
+    for g in range(x0.shape[0]):
+        h = lib.ref_create()
+        name = str(tmp_path / f"ref_{g}.log").encode()
+        lib.ref_reset(h, 0.05, ws, np.ascontiguousarray(x0[g]).ctypes.data_as(dp), 0.0, 1, name, g + 1, 0.1, 0.5, 1.0, 0.5, None)
+        a = np.ascontiguousarray(full_actions[g].reshape(-1, 8))
+        lib.ref_rollout(h, a.ctypes.data_as(dp), a.shape[0], None, None)
+        lib.ref_destroy(h)
+        out.append(open(name.decode(), "rb").read())
+    return out
+
+
+def test_batched_log_writer_matches_reference_files(rgs, tmp_path):
+    """BatchedGameSim.write_logs -> rgs_write_logs: 16 games logged every step by the batched path give the SAME
+    BYTES as the compiled reference's own Logger for each game (29-double records, src/GameSim.cpp:161-170, incl. the
+    damage.row(k) quirk of include/utils.h:75, and a decided game's log stopping at its last live step); the
+    layout flag changes only the damage fields 14..29 (true rows)."""
+    if tl.ref_lib() is None:
+        pytest.skip("needs the compiled reference (oracle/_ref)")
+    n, steps, hold, ws = 16, 120, 10, 1
+    x0, acts = tl.synth_inputs(9, 0, n, 2, steps // hold)
+    x0[0] = (4.0, 0.0, 5.0, 0.0)                      # KAT1: decided at step 5 -> a short log
+    acts[1, :, 0] = (0.0, -10.0)                      # KAT4-like head-on impact: damage fields are non-zero
+    acts[1, :, 1] = (0.0, 10.0)
+    full = np.repeat(acts, hold, axis=1)             # [n, steps, 4, 2]
+    ref = _reference_logs(tmp_path, x0, full, ws=ws)
+    sim = rgs.BatchedGameSim(n, mode="exact", winning_score=ws)
+    sim.reset(x0_ball=torch.from_numpy(x0).cuda())
+    traj = sim.run(torch.from_numpy(acts).cuda(), n_steps=steps, hold=hold, log_stride=1)
+    live = sim.events()[:, tl.EV["LIVE_STEPS"]]
+    sim.write_logs(traj, str(tmp_path / "mine_{}.log"), first_index=1, layout="reference", n_records=live)
+    for g in range(n):
+        mine = open(tmp_path / f"mine_{g + 1}.log", "rb").read()
+        assert mine == ref[g], g
+    assert len(ref[0]) == 5 * 29 * 8 and len(ref[2]) == steps * 29 * 8
+    sim.write_logs(traj, str(tmp_path / "rm_{}.log"), first_index=1, layout="row_major", n_records=live)
+    a = np.fromfile(tmp_path / "mine_2.log").reshape(-1, 29)
+    b = np.fromfile(tmp_path / "rm_2.log").reshape(-1, 29)
+    assert np.array_equal(a[:, :13], b[:, :13]) and not np.array_equal(a[:, 13:], b[:, 13:])
+    dm = sim.damage()[1].cpu().numpy()              # (aggressor, victim)
+    assert dm[0, 1] > 0 and np.array_equal(b[-1, 13:].reshape(4, 4), dm)
+    # append mode: two launches of 60 steps give the same files as one of 120
+    sim.reset(x0_ball=torch.from_numpy(x0).cuda())
+    t1 = sim.run(torch.from_numpy(acts[:, :6]).cuda(), n_steps=60, hold=hold, log_stride=1)
+    l1 = sim.events()[:, tl.EV["LIVE_STEPS"]]
+    sim.write_logs(t1, str(tmp_path / "two_{}.log"), n_records=l1)
+    t2 = sim.run(torch.from_numpy(np.ascontiguousarray(acts[:, 6:])).cuda(), n_steps=60, hold=hold, log_stride=1)
+    sim.write_logs(t2, str(tmp_path / "two_{}.log"), n_records=sim.events()[:, tl.EV["LIVE_STEPS"]] - l1, append=True)
+    for g in range(n):
+        assert open(tmp_path / f"two_{g + 1}.log", "rb").read() == ref[g]
+    with pytest.raises(ValueError):
+        sim.write_logs(traj, str(tmp_path / "no_placeholder.log"))
+
+
+def test_damage_statistics_on_device(rgs):
+    """K4 sums the damage matrix over the batch in fixed point (one integer all-reduce vector): equal to the sum of
+    the per-game matrices to the fixed-point resolution, in exact and fast mode."""
+    n, steps, hold = 20000, 100, 10
+    for mode in ("exact", "fast"):
+        sim = rgs.BatchedGameSim(n, mode=mode, winning_score=4)
+        x0, acts = rgs.synth_inputs(n, steps // hold, seed=13, dtype=sim.action_dtype)
+        sim.reset(x0_ball=x0)
+        sim.run(acts, n_steps=steps, hold=hold)
+        d = rgs.stats_to_dict(sim.stats())
+        dm = sim.damage().cpu().numpy()
+        assert dm.sum() > 1.0
+        assert np.abs(d["damage_sum"] - dm.sum(0)).max() <= n * 2.0 ** -24
+        assert np.all(np.diag(d["damage_sum"]) == 0)
+        team = np.array([[dm[:, :2, :2].sum(), dm[:, :2, 2:].sum()], [dm[:, 2:, :2].sum(), dm[:, 2:, 2:].sum()]])
+        assert np.abs(d["damage_team_sum"] - team).max() <= 4 * n * 2.0 ** -24
+        assert d["overlap_fixes"] == int(sim.events()[:, 15].sum())
+
+
+def test_monte_carlo_reference_signature(rgs, tmp_path):
+    """robo_game_sim_b200.monte_carlo(mc_params, team_A_run_method, team_B_run_method, cbf_run_method=None) -- the
+    reference's signature (py/MonteCarlo.py:8) and artefacts.  Sequential (reference order, per-game SimState views),
+    lock-step batched and on-device paths; the logs of the first two are the compiled reference's bytes."""
+    import types
+
+    mc = types.SimpleNamespace(num_runs=3, T=2.0, dt=0.05, winning_score=4, x0_ball=np.array([-1.0, 0.5, 2.0, 1.0]),
+                               noise_stdev=0.0, tau_puck=0.1, tau_player=0.5, player_mass=1.0, puck_mass=0.5,
+                               log_prefix=str(tmp_path / "seq"), input_limit=10.0, safety_radius=0.4, barrier_gain=30)
+
+    def chase(team):        # a stateless controller: both players head for the puck
+        def run(sim_state):
+            assert isinstance(sim_state, rgs.SimState)
+            pk = sim_state.get_puck_pos()
+            return tuple(np.clip(4.0 * (pk - sim_state.get_player_pos(team, k)), -10, 10) for k in (1, 2))
+        return run
+
+    def damp(u_nominal, sim_state):   # a stand-in for CBF.get_centralized_safe_control...: scales the commands
+        return [0.5 * u for u in u_nominal]
+
+    out = rgs.monte_carlo(mc, chase("A"), chase("B"), damp, verbose=False)
+    assert out["games"] == 3 and sorted(os.listdir(mc.log_prefix)) == ["configuration.txt", "mc_run_1.log", "mc_run_2.log", "mc_run_3.log"]
+    assert len(open(os.path.join(mc.log_prefix, "configuration.txt")).read().splitlines()) == 13
+    seq = [open(os.path.join(mc.log_prefix, f"mc_run_{i}.log"), "rb").read() for i in (1, 2, 3)]
+    assert len(seq[0]) == 41 * 29 * 8 and seq[0] == seq[1] == seq[2]          # noise = 0: the runs are one game
+    # the same loop against the compiled reference
+    lib = tl.ref_lib()
+    if lib is not None:
+        dp = C.POINTER(C.c_double)
+        h = lib.ref_create()
+        name = str(tmp_path / "ref.log").encode()
+        st = np.zeros(22)
+        lib.ref_reset(h, mc.dt, 4, mc.x0_ball.ctypes.data_as(dp), 0.0, 1, name, 1, 0.1, 0.5, 1.0, 0.5, None)
+        lib.ref_run(h, np.zeros(8).ctypes.data_as(dp), st.ctypes.data_as(dp))
+        a, b = chase("A"), chase("B")
+        for _ in range(40):
+            ss = rgs.SimState(st)
+            u = np.concatenate(damp([*a(ss), *b(ss)], ss))
+            lib.ref_run(h, np.ascontiguousarray(u).ctypes.data_as(dp), st.ctypes.data_as(dp))
+        lib.ref_destroy(h)
+        assert open(name.decode(), "rb").read() == seq[0]
+    # lock-step batched path: same controllers on [n, 22] views, exact mode -> the same files
+    mc.log_prefix = str(tmp_path / "bat")
+    out_b = rgs.monte_carlo(mc, chase("A"), chase("B"), damp, batched=True, verbose=False)
+    assert [open(os.path.join(mc.log_prefix, f"mc_run_{i}.log"), "rb").read() for i in (1, 2, 3)] == seq
+    for k in ("games", "wins_a", "wins_b", "lead_a", "lead_b"):
+        assert out_b[k] == out[k]
+    assert np.allclose(out_b["damage_sum"], out["damage_sum"], atol=1e-6)
+    # on-device teams: one launch per Monte Carlo run set, logs of n_steps + 1 records
+    mc.log_prefix, mc.num_runs = str(tmp_path / "dev"), 8
+    out_d = rgs.monte_carlo(mc, "classical", "classical", "cbf", verbose=False)
+    assert out_d["games"] == 8
+    rec = np.fromfile(os.path.join(mc.log_prefix, "mc_run_8.log")).reshape(-1, 29)
+    assert rec.shape[0] == 41 and np.allclose(rec[:, 0], 0.05 * np.arange(1, 42)) and np.isfinite(rec).all()
+    with pytest.raises(ValueError):
+        rgs.monte_carlo(mc, "classical", "dmpc", verbose=False)
+
+
 # ------------------------------------------------------------------ K3: shared-state rollout sampling
 def test_rollout_sampler_matches_oracle(rgs):
     """BASELINE configs[4]: 4096 candidate command sequences x 50 steps from ONE state.  fp64 parity mode:
