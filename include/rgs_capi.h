@@ -73,11 +73,13 @@ typedef struct rgs_params {
     double dt;                /* 0.05 */
     int32_t winning_score;    /* reset() argument */
     int32_t players_per_team; /* 2 = reference; up to RGS_MAX_TEAM */
-    double noise;             /* process-noise stdev; must be 0 in RGS_MODE_EXACT_F64 */
+    double noise;             /* process-noise stdev w_stdev_ (reset() argument, src/GameSim.cpp:30,66-67); FAST modes
+                               * only (statistical, not bitwise: libstdc++'s normal stream is implementation-defined);
+                               * must be 0 in RGS_MODE_EXACT_F64 */
     double tau_puck, tau_player, player_mass, puck_mass;
     double arena_x, arena_y, player_radius, puck_radius, goal_height; /* 10, 5, 0.2, 0.175, 1.0 */
     int32_t mode;             /* RGS_MODE_* */
-    int32_t reserved;
+    int32_t seed;             /* reset()'s seed (src/GameSim.cpp:41): keys the noise streams together with the GLOBAL game index */
 } rgs_params;
 
 typedef struct rgs_batch rgs_batch; /* opaque: N independent games resident on one GPU */
@@ -93,7 +95,12 @@ int rgs_device_count(int *out);
 /* replaces: GameSim::GameSim() (reference src/GameSim.cpp:3-17) for n_games games at once. */
 int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_params *p);
 int rgs_batch_destroy(rgs_batch *b);
-int rgs_batch_set_params(rgs_batch *b, const rgs_params *p); /* n_games, team size and mode are fixed */
+int rgs_batch_set_params(rgs_batch *b, const rgs_params *p);
+
+/* Global index of game 0 of this batch (default 0).  Every per-game random stream (process noise) is keyed by
+ * (params.seed, game_offset + g), so a Monte Carlo batch sharded over several GPUs draws the same numbers as the
+ * same runs on one GPU (py/MonteCarlo.py:28-30 seeds run i with i). */
+int rgs_batch_set_game_offset(rgs_batch *b, int64_t first_game); /* n_games, team size and mode are fixed */
 
 /* replaces: GameSim::reset (reference src/GameSim.cpp:21-55) -- K5.
  *   d_x0_ball [n_games,4] doubles (x0_stride doubles between games; 0 = one puck state shared by

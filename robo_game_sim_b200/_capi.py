@@ -26,7 +26,7 @@ class RgsParams(C.Structure):
                 ("noise", C.c_double), ("tau_puck", C.c_double), ("tau_player", C.c_double),
                 ("player_mass", C.c_double), ("puck_mass", C.c_double), ("arena_x", C.c_double),
                 ("arena_y", C.c_double), ("player_radius", C.c_double), ("puck_radius", C.c_double),
-                ("goal_height", C.c_double), ("mode", C.c_int32), ("reserved", C.c_int32)]
+                ("goal_height", C.c_double), ("mode", C.c_int32), ("seed", C.c_int32)]
 
 
 class RgsPolicy(C.Structure):
@@ -47,6 +47,7 @@ SIGNATURES = {
     "rgs_batch_create": (C.c_int, [C.POINTER(_vp), C.c_int, _i64, _PP]),
     "rgs_batch_destroy": (C.c_int, [_vp]),
     "rgs_batch_set_params": (C.c_int, [_vp, _PP]),
+    "rgs_batch_set_game_offset": (C.c_int, [_vp, _i64]),
     "rgs_batch_reset": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "rgs_batch_run": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp, _vp]),
     "rgs_batch_run_synth": (C.c_int, [_vp, _u64, _i64, _i64, _i64, _dbl, _i64, _i64, _vp, _vp]),

@@ -54,10 +54,11 @@ int check_params(const rgs_params *p) {
     if (!(p->player_mass > 0.0) || !(p->puck_mass > 0.0)) return fail(RGS_EINVAL, "masses must be > 0");
     if (!(p->arena_x > 0.0) || !(p->arena_y > 0.0) || !(p->player_radius > 0.0) || !(p->puck_radius > 0.0))
         return fail(RGS_EINVAL, "arena and radii must be > 0");
-    if (p->noise != 0.0)
+    if (!(p->noise >= 0.0)) return fail(RGS_EINVAL, "noise must be >= 0");
+    if (p->noise != 0.0 && p->mode == RGS_MODE_EXACT_F64)
         return fail(RGS_EUNSUPPORTED,
-                    "process noise is not implemented: every shipped reference script runs noise=0 and the "
-                    "reference's libstdc++ normal_distribution stream is not reproducible bit for bit");
+                    "process noise runs in the FAST modes (statistical parity): the reference's libstdc++ "
+                    "normal_distribution stream is implementation-defined, so a bit-exact noisy mode does not exist");
     return RGS_OK;
 }
 
@@ -76,7 +77,9 @@ struct rgs_batch {
     // K2 per-lane scratch (correctOverlap tracks, rgs_lane.cuh), one per stream a rollout can be in flight on:
     // [0] the caller's stream, [1], [2] the two private streams of rgs_batch_run_host; allocated on first use
     void *lane_scratch[3] = {nullptr, nullptr, nullptr};
-    size_t lane_scratch_bytes = 0;
+    size_t lane_scratch_cap[3] = {0, 0, 0};
+    size_t lane_scratch_need[2] = {0, 0};  // [noise-free, noise] kernels, queried on first use
+    int64_t game_offset = 0;               // global index of game 0 (keys the process-noise streams)
     // staging for rgs_batch_run_host
     void *stage_actions = nullptr;
     size_t stage_actions_bytes = 0;
@@ -129,19 +132,28 @@ int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64
                                 b->pol.barrier_gain, b->pol.cbf, b->pol.sweeps, b->pol.kind};
     }
     if (b->p.mode != RGS_MODE_EXACT_F64) {
-        if (b->lane_scratch_bytes == 0) {
-            cudaError_t qe = rgs::lane_scratch_bytes(b->n_team, b->p.mode == RGS_MODE_FAST_F64, b->sm_count, &b->lane_scratch_bytes);
+        const int nz = b->p.noise != 0.0 ? 1 : 0;
+        if (b->lane_scratch_need[nz] == 0) {
+            cudaError_t qe = rgs::lane_scratch_bytes(b->n_team, b->p.mode == RGS_MODE_FAST_F64, nz, b->sm_count, &b->lane_scratch_need[nz]);
             if (qe != cudaSuccess) return cuda_fail(qe, "lane scratch size query");
         }
-        if (!b->lane_scratch[slot]) {
-            cudaError_t me = cudaMalloc(&b->lane_scratch[slot], b->lane_scratch_bytes);
+        if (b->lane_scratch_cap[slot] < b->lane_scratch_need[nz]) {
+            if (b->lane_scratch[slot]) {   // a batch switched to the (larger) noise kernels: in-flight work first
+                RGS_CUDA(cudaDeviceSynchronize());
+                cudaFree(b->lane_scratch[slot]);
+                b->lane_scratch[slot] = nullptr;
+                b->lane_scratch_cap[slot] = 0;
+            }
+            cudaError_t me = cudaMalloc(&b->lane_scratch[slot], b->lane_scratch_need[nz]);
             if (me != cudaSuccess) {
                 cudaGetLastError();
-                return fail(RGS_ENOMEM, "lane scratch of %zu bytes: %s", b->lane_scratch_bytes, cudaGetErrorString(me));
+                return fail(RGS_ENOMEM, "lane scratch of %zu bytes: %s", b->lane_scratch_need[nz], cudaGetErrorString(me));
             }
+            b->lane_scratch_cap[slot] = b->lane_scratch_need[nz];
         }
         A.lane_scratch = b->lane_scratch[slot];
-        A.lane_scratch_bytes = b->lane_scratch_bytes;
+        A.lane_scratch_bytes = b->lane_scratch_cap[slot];
+        A.noise_game0 = b->game_offset + g0;
     }
     cudaError_t e;
     switch (b->p.mode) {
@@ -283,6 +295,12 @@ int rgs_batch_set_params(rgs_batch *b, const rgs_params *p) {
     if (p->players_per_team != b->n_team) return fail(RGS_EINVAL, "players_per_team is fixed at create time");
     if (p->mode != b->p.mode) return fail(RGS_EINVAL, "mode is fixed at create time");
     b->p = *p;
+    return RGS_OK;
+}
+
+int rgs_batch_set_game_offset(rgs_batch *b, int64_t first_game) {
+    if (!b) return fail(RGS_EINVAL, "batch is NULL");
+    b->game_offset = first_game;
     return RGS_OK;
 }
 
@@ -554,7 +572,8 @@ int rgs_write_logs(const double *h_traj, int64_t n_games, int64_t n_rec, int32_t
 // ---- batch-of-one handle behind robo_game_py.GameSim -----------------------------------------
 struct rgs_single {
     int device = 0;
-    rgs_batch *b = nullptr;
+    rgs_batch *b = nullptr;        // the batch of the current game: b_exact (K1) or, with process noise, b_noise (K2 fp64)
+    rgs_batch *b_exact = nullptr, *b_noise = nullptr;
     rgs_params p{};
     double *d_act = nullptr, *d_x0 = nullptr;
     double *h_pin = nullptr;  // pinned scratch: [0..21] state, [22..29] actions, [30] clock, [32..47] damage
@@ -573,8 +592,9 @@ int rgs_single_create(rgs_single **out, int device) {
     if (!s) return fail(RGS_ENOMEM, "out of host memory");
     s->device = device;
     rgs_default_params(&s->p);
-    int rc = rgs_batch_create(&s->b, device, 1, &s->p);
+    int rc = rgs_batch_create(&s->b_exact, device, 1, &s->p);
     if (rc != RGS_OK) { delete s; return rc; }
+    s->b = s->b_exact;
     DeviceGuard guard(device);
     cudaError_t e = cudaMalloc(&s->d_act, 8 * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_x0, 4 * sizeof(double));
@@ -595,7 +615,8 @@ int rgs_single_destroy(rgs_single *s) {
         if (s->h_pin) cudaFreeHost(s->h_pin);
     }
     if (s->log) fclose(s->log);
-    rgs_batch_destroy(s->b);
+    rgs_batch_destroy(s->b_exact);
+    rgs_batch_destroy(s->b_noise);
     delete s;
     return RGS_OK;
 }
@@ -603,13 +624,21 @@ int rgs_single_destroy(rgs_single *s) {
 int rgs_single_reset(rgs_single *s, double dt, int32_t winning_score, const double *h_x0_ball, double noise, int32_t log,
                      const char *logname, int32_t seed, double tau_puck, double tau_player, double player_mass,
                      double puck_mass, double *h_out_state22) {
-    (void)seed;  // the seed only feeds the process-noise stream, which is identically scaled by noise = 0
     if (!s) return fail(RGS_EINVAL, "handle is NULL");
     if (!h_x0_ball) return fail(RGS_EINVAL, "x0_ball is NULL");
     rgs_params p = s->p;
     p.dt = dt;
     p.winning_score = winning_score;
     p.noise = noise;
+    p.seed = seed;   // reng_ = std::default_random_engine(seed), src/GameSim.cpp:41
+    // noise = 0 (every shipped reference script): the event-exact fp64 kernel K1.  noise > 0: the K2 formulation in
+    // fp64 with Philox process noise -- statistically, not bitwise, the reference's (its normal stream is libstdc++'s)
+    p.mode = noise != 0.0 ? RGS_MODE_FAST_F64 : RGS_MODE_EXACT_F64;
+    if (noise != 0.0 && !s->b_noise) {
+        int rcn = rgs_batch_create(&s->b_noise, s->device, 1, &p);
+        if (rcn != RGS_OK) return rcn;
+    }
+    s->b = noise != 0.0 ? s->b_noise : s->b_exact;
     p.tau_puck = tau_puck;
     p.tau_player = tau_player;
     p.player_mass = player_mass;

@@ -80,6 +80,7 @@ struct RunArgs {
     // K2 lane kernel: per-resident-lane global scratch (correctOverlap tracks + jam snapshot, rgs_lane.cuh)
     void *lane_scratch;
     size_t lane_scratch_bytes;
+    int64_t noise_game0;   // global index of game 0 of this launch for the process-noise streams
 };
 
 // ---- Philox4x32-10 (Salmon et al. 2011), counter-based: keyed by (seed, game, action index) ----

@@ -32,7 +32,65 @@ struct FastParams {
     T tab_k[2][kCols];      // a (1-R^i)/(1-R)
     T lim_x[2], lim_y[2];   // arena/2 - r (folded wall-overlap limits for the register phase)
     T lim_x_in[2], lim_y_in[2];  // largest value strictly below lim (lane kernel: a corrected body never rests ON the limit)
+    // process noise on the player accelerations (reference src/GameSim.cpp:62-68), see NoiseCoef below; all scaled by sigma
+    T noise;                     // sigma = w_stdev_ (0: none)
+    T nz_sub[3];                 // Cholesky factor {l11, l21, l22} of the (dv, dp) increment of ONE sub-step (h = dt_col)
+    T nz_end[3];                 // same for the noise accumulated over a whole game-step (50 sub-steps)
+    T nz_env;                    // 6.5 standard deviations of the accumulated position noise (broad-phase envelope)
+    uint32_t seed_lo, seed_hi;   // reset()'s seed
 };
+
+// The reference adds sigma * N(0,1) to both player accelerations on EVERY f_player call, i.e. on each of the four
+// stages of each RK4 sub-step (:66-67, :73-85).  The dynamics are linear, so the four stage draws e1..e4 of one axis
+// enter the sub-step result linearly (z = -h / tau):
+//   dv = (h/6)   [ e1 (1 + z + z^2/2 + z^3/4) + e2 (2 + z + z^2/2) + e3 (2 + z) + e4 ]
+//   dp = (h^2/6) [ e1 (1 + z/2 + z^2/4)       + e2 (1 + z/2)       + e3 ]
+// -- a 2-D Gaussian increment per sub-step and axis, sampled EXACTLY with two normals (Cholesky factor l11, l21, l22
+// of its covariance) instead of the four stage draws.  Per unit sigma.
+template <typename T>
+struct NoiseCoef { T l11, l21, l22; };
+template <typename T>
+__host__ __device__ inline NoiseCoef<T> noise_coef(T h, T neg_inv_tau) {
+    const T z = h * neg_inv_tau;
+    const T c1 = T(1) + z + z * z * T(0.5) + z * z * z * T(0.25), c2 = T(2) + z + z * z * T(0.5), c3 = T(2) + z, c4 = T(1);
+    const T d1 = T(1) + z * T(0.5) + z * z * T(0.25), d2 = T(1) + z * T(0.5), d3 = T(1);
+    const T sv = h / T(6), sp = h * h / T(6);
+    const T qvv = sv * sv * (c1 * c1 + c2 * c2 + c3 * c3 + c4 * c4);
+    const T qpp = sp * sp * (d1 * d1 + d2 * d2 + d3 * d3);
+    const T qpv = sv * sp * (c1 * d1 + c2 * d2 + c3 * d3);
+    NoiseCoef<T> r;
+    r.l11 = T(sqrt(qvv));
+    r.l21 = r.l11 > T(0) ? qpv / r.l11 : T(0);
+    const T rem = qpp - r.l21 * r.l21;
+    r.l22 = rem > T(0) ? T(sqrt(rem)) : T(0);
+    return r;
+}
+
+// four independent standard normals from one Philox4x32-10 block (Box-Muller), keyed by the reset seed and counted
+// by (global game index, game-step, draw id)
+RGS_DEV void box_muller(uint32_t a, uint32_t b, float &g0, float &g1) {
+    const float u1 = ((float)(a >> 8) + 1.0f) * 5.9604645e-8f;   // (0, 1]
+    const float u2 = (float)(b >> 8) * 5.9604645e-8f;            // [0, 1)
+    const float r = sqrtf(-2.0f * logf(u1));
+    const float th = 6.2831853071795865f * u2;
+    g0 = r * cosf(th);
+    g1 = r * sinf(th);
+}
+RGS_DEV void box_muller(uint32_t a, uint32_t b, double &g0, double &g1) {
+    const double u1 = ((double)a + 1.0) * 2.3283064365386963e-10;
+    const double u2 = (double)b * 2.3283064365386963e-10;
+    const double r = sqrt(-2.0 * log(u1));
+    const double th = 6.2831853071795865 * u2;
+    g0 = r * cos(th);
+    g1 = r * sin(th);
+}
+template <typename T>
+RGS_DEV void normals4(uint32_t seed_lo, uint32_t seed_hi, long long game, uint32_t step, uint32_t id, T g[4]) {
+    uint32_t o[4];
+    philox4x32_10((uint32_t)game, (uint32_t)((unsigned long long)game >> 32), step, id, seed_lo, seed_hi ^ 0x4E5A4E5Au, o);
+    box_muller(o[0], o[1], g[0], g[1]);
+    box_muller(o[2], o[3], g[2], g[3]);
+}
 
 // advance one axis by an arbitrary h (time-of-impact split), same RK4 polynomial
 template <typename T>

@@ -93,6 +93,27 @@ inline FastParams<T> make_fast_params(const rgs_params &p) {
         f.lim_x_in[ty] = std::nextafter(f.lim_x[ty], T(0));
         f.lim_y_in[ty] = std::nextafter(f.lim_y[ty], T(0));
     }
+    {   // process noise (players only): per-sub-step increment and its accumulation over the 50 sub-steps of a step,
+        // covariance recurrence S' = M S M^T + Q with M = [[R, 0], [a, 1]] in (v, p) order, evaluated in fp64
+        const double sg = p.noise, hd = (double)h, nit = -1.0 / p.tau_player;
+        const NoiseCoef<double> q = noise_coef<double>(hd, nit);
+        const double z = hd * nit, qq = 1.0 + z / 2 + z * z / 6 + z * z * z / 24, R = 1.0 + z * qq, a = hd * qq;
+        const double Qvv = q.l11 * q.l11, Qpv = q.l21 * q.l11, Qpp = q.l21 * q.l21 + q.l22 * q.l22;
+        double Svv = 0, Spv = 0, Spp = 0;
+        for (int i = 0; i < RGS_GRID_POINTS; ++i) {
+            const double nvv = R * R * Svv + Qvv;
+            const double npv = R * (a * Svv + Spv) + Qpv;
+            const double npp = a * a * Svv + 2 * a * Spv + Spp + Qpp;
+            Svv = nvv; Spv = npv; Spp = npp;
+        }
+        const double e11 = std::sqrt(Svv), e21 = e11 > 0 ? Spv / e11 : 0.0, e22 = std::sqrt(std::fmax(0.0, Spp - e21 * e21));
+        f.noise = T(sg);
+        f.nz_sub[0] = T(sg * q.l11); f.nz_sub[1] = T(sg * q.l21); f.nz_sub[2] = T(sg * q.l22);
+        f.nz_end[0] = T(sg * e11); f.nz_end[1] = T(sg * e21); f.nz_end[2] = T(sg * e22);
+        f.nz_env = T(6.5 * std::fabs(sg) * std::sqrt(Spp));
+        f.seed_lo = (uint32_t)p.seed;
+        f.seed_hi = 0x5EEDu;
+    }
     return f;
 }
 

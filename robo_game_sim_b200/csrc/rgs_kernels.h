@@ -15,7 +15,7 @@ cudaError_t launch_rollout_exact(int n_team, const DevParams<double> &P, const R
 // lane_scratch_bytes() bytes of device memory that no other launch in flight uses.
 cudaError_t launch_rollout_lane_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
 cudaError_t launch_rollout_lane_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count);
-cudaError_t lane_scratch_bytes(int n_team, int fp64, int sm_count, size_t *bytes);
+cudaError_t lane_scratch_bytes(int n_team, int fp64, int noise, int sm_count, size_t *bytes);
 
 // K4: per-batch statistics vector int64[RGS_N_STATS] (rgs_aux_kernels.cu)
 cudaError_t launch_stats(int n_team, int64_t n_games, const double *state, const long long *events, const double *damage,

@@ -73,13 +73,19 @@ struct LaneScratch {
     static constexpr int FL = E;         // [e] column of the last correctOverlap fix (= CS when none)
     static constexpr int QI = 2 * E;     // [e] (seq << 12) | (col << 6)... see q_pack
     static constexpr int FF = 3 * E;     // [e] column of the first correctOverlap fix (= CS when none)
-    static constexpr int TS = 4 * E;     // [e] checksum of the track words written for this segment (jam detection)
-    static constexpr int EVC = 5 * E;    // [k] event counters of this launch (RGS_EV_* order; [RGS_EV_HASH], [16] = hash lo, hi)
-    static constexpr int NI = 5 * E + 17;
-    // per-lane global scratch area, in T-sized words: the tracks, then the jam snapshot (LaneGame::JamSnap)
+    static constexpr int NI = 4 * E;
+    // per-lane global scratch area, in T-sized words ([word][lane] inside a warp): the tracks; the event counters of
+    // this launch (RGS_EV_* order; [RGS_EV_HASH], [16] = hash lo, hi) and the per-body checksum of the track words
+    // written for the segment (jam detection) as ints; then the jam snapshot (LaneGame::JamSnap).  All of it is touched
+    // by the event path only -- the shared-memory record above is sized for 4 resident 128-lane CTAs per SM.
     static constexpr int TRK_WORDS = 2 * E * kCols;
+    static constexpr int EVC = TRK_WORDS, TS = EVC + 17;
+    static constexpr int JAM0 = TS + E;
     static constexpr int JAM_F = QT + E, JAM_I = 5 * E + 17 + 3 * kJamLog;
-    static constexpr int SCR_WORDS = TRK_WORDS + JAM_F + JAM_I;
+    static constexpr int SCR_WORDS = JAM0 + JAM_F + JAM_I;
+    // process-noise kernels only: accumulated noise (dpx, dpy, dvx, dvy) since the segment start of player e at column c
+    static constexpr int NZ0 = SCR_WORDS, NZ_WORDS = 4 * (E - 1) * kCols;
+    static constexpr int SCR_WORDS_NOISE = SCR_WORDS + NZ_WORDS;
     T *f;
     int *i;
     int stride;
@@ -88,6 +94,7 @@ struct LaneScratch {
     RGS_DEV T &TR(int e, int c, int a) const { return trk[(size_t)((e * kCols + c) * 2 + a) * tstride]; }
     RGS_DEV T &F(int w) const { return f[w * stride]; }
     RGS_DEV int &I(int w) const { return i[w * stride]; }
+    RGS_DEV int &G(int w) const { return *reinterpret_cast<int *>(&trk[(size_t)w * tstride]); }   // int word of the global area
 };
 
 // index of the lowest set bit of a non-zero mask
@@ -179,7 +186,7 @@ template <typename T> struct Slack;
 template <> struct Slack<float> { static constexpr float v = 2.0e-4f; };
 template <> struct Slack<double> { static constexpr double v = 1.0e-9; };
 
-template <typename T, int NT>
+template <typename T, int NT, bool kNoise = false>
 struct LaneGame {
     static constexpr int E = 2 * NT + 1, PK = 2 * NT, NP = 2 * NT, NPAIR = E * (E - 1) / 2;
     using S = LaneScratch<T, NT>;
@@ -205,6 +212,41 @@ struct LaneGame {
     }
     RGS_DEV bool in_step(T t) const { return since_t0(t) < P.d.dt; }
 
+    // ---- process noise (kNoise instantiations; reference src/GameSim.cpp:62-68, see rgs_fast.cuh NoiseCoef) ----
+    // Every segment of a player carries its own accumulated-noise path NZ(e, c, .) over the columns after its start
+    // (the reference draws fresh noise whenever it re-integrates a body, :285-297, :329-340).  A step without
+    // broad-phase flags needs only the end of the path, drawn directly from the accumulated 2-D Gaussian.
+    mutable long long nz_game = 0;        // global game index
+    mutable unsigned nz_step = 0, nz_epoch = 0;
+    mutable bool nz_on = false;           // false while a quiet step commits from the closed form
+    RGS_DEV T &NZ(int e, int c, int k) const { return s.trk[(size_t)(S::NZ0 + (e * kCols + c) * 4 + k) * s.tstride]; }
+    RGS_DEV void gen_noise_path(int e, int c0) const {
+        T npx = T(0), npy = T(0), nvx = T(0), nvy = T(0);
+        NZ(e, c0, 0) = T(0); NZ(e, c0, 1) = T(0); NZ(e, c0, 2) = T(0); NZ(e, c0, 3) = T(0);
+        const T R = tab->e[0][1].g, k1 = tab->e[0][1].k;
+#pragma unroll 1
+        for (int c = c0 + 1; c <= kGrid; ++c) {
+            T g[4];
+            normals4<T>(P.seed_lo, P.seed_hi, nz_game, nz_step, ((nz_epoch + 1u) << 16) | ((unsigned)e << 8) | (unsigned)c, g);
+            npx = npx + k1 * nvx + fm(P.nz_sub[1], g[0], P.nz_sub[2] * g[1]);
+            npy = npy + k1 * nvy + fm(P.nz_sub[1], g[2], P.nz_sub[2] * g[3]);
+            nvx = fm(R, nvx, P.nz_sub[0] * g[0]);
+            nvy = fm(R, nvy, P.nz_sub[0] * g[2]);
+            NZ(e, c, 0) = npx; NZ(e, c, 1) = npy; NZ(e, c, 2) = nvx; NZ(e, c, 3) = nvy;
+        }
+    }
+    // noise of one RK4 call of arbitrary length h (the two pieces around a time of impact, :255-256, :287-288)
+    RGS_DEV void noise_kick(int e, int piece, T h, T &px, T &py, T &vx, T &vy) const {
+        if (!(h > T(0))) return;
+        const NoiseCoef<T> q = noise_coef<T>(h, P.neg_inv_tau[0]);
+        T g[4];
+        normals4<T>(P.seed_lo, P.seed_hi, nz_game, nz_step, ((nz_epoch + 1u) << 16) | ((unsigned)e << 8) | (0xF0u + (unsigned)piece), g);
+        px += P.noise * fm(q.l21, g[0], q.l22 * g[1]);
+        py += P.noise * fm(q.l21, g[2], q.l22 * g[3]);
+        vx += P.noise * (q.l11 * g[0]);
+        vy += P.noise * (q.l11 * g[2]);
+    }
+
     // cumulative correctOverlap offset of body e at column c > CS[e]
     RGS_DEV void off_at(int e, int c, T &ox, T &oy) const {
         if (c >= s.I(S::FL + e)) { ox = s.F(S::OFF + 2 * e); oy = s.F(S::OFF + 2 * e + 1); }
@@ -225,28 +267,29 @@ struct LaneGame {
         const T ox = s.F(S::OFF + 2 * e), oy = s.F(S::OFF + 2 * e + 1);
         if (fl == s.I(S::CS + e)) {
             s.I(S::FF + e) = c;
+            s.G(S::TS + e) = 0;   // (the checksum only means something once the segment has been fixed twice)
         } else {
-            int ts = s.I(S::TS + e);
+            int ts = s.G(S::TS + e);
 #pragma unroll 1
             for (int k = fl; k < c; ++k) {
                 s.TR(e, k, 0) = ox; s.TR(e, k, 1) = oy;
                 ts = ts * 31 + (word_bits(ox) ^ (word_bits(oy) * 7) ^ k);
             }
-            s.I(S::TS + e) = ts;
+            s.G(S::TS + e) = ts;
         }
         s.F(S::OFF + 2 * e) = ox + fx; s.F(S::OFF + 2 * e + 1) = oy + fy;
         s.I(S::FL + e) = c;
     }
 
     // event record of the launch: counters in the scratch record, flushed to the game's int64 record at the end
-    RGS_DEV void ev_add(int k, int n = 1) const { s.I(S::EVC + k) += n; }
+    RGS_DEV void ev_add(int k, int n = 1) const { s.G(S::EVC + k) += n; }
     RGS_DEV void hash_ev(long long live, int kind, int i, int j, int goal) const {
-        unsigned long long h = ((unsigned long long)(unsigned)s.I(S::EVC + 16) << 32) | (unsigned)s.I(S::EVC + RGS_EV_HASH);
+        unsigned long long h = ((unsigned long long)(unsigned)s.G(S::EVC + 16) << 32) | (unsigned)s.G(S::EVC + RGS_EV_HASH);
         h ^= ((unsigned long long)live << 16) | ((unsigned long long)kind << 12) | ((unsigned long long)i << 8) |
              ((unsigned long long)(j < 0 ? 15 : j) << 4) | (unsigned long long)goal;   // == hash_event() of rgs_device.cuh
         h *= 0x100000001B3ULL;
-        s.I(S::EVC + RGS_EV_HASH) = (int)(unsigned)h;
-        s.I(S::EVC + 16) = (int)(unsigned)(h >> 32);
+        s.G(S::EVC + RGS_EV_HASH) = (int)(unsigned)h;
+        s.G(S::EVC + 16) = (int)(unsigned)(h >> 32);
     }
 
     // state of body e at column c >= CS[e]-1 (position includes the correctOverlap offsets)
@@ -269,6 +312,8 @@ struct LaneGame {
         py = fm(wy, k, fm(uy, tj, spy)) + oy;
         vx = fm(wx, g, ux);
         vy = fm(wy, g, uy);
+        if constexpr (kNoise)
+            if (nz_on && e != PK) { px += NZ(e, c, 0); py += NZ(e, c, 1); vx += NZ(e, c, 2); vy += NZ(e, c, 3); }
     }
 
     // start a new segment of body e at column c with state (px,py,vx,vy); prev = state at c-1
@@ -279,7 +324,8 @@ struct LaneGame {
         s.I(S::CS + e) = c;
         s.I(S::FL + e) = c;
         s.I(S::FF + e) = c;
-        s.I(S::TS + e) = 0;
+        if constexpr (kNoise)
+            if (e != PK) gen_noise_path(e, c);
     }
 
     // bounding interval of body e over columns CS[e]..50 (monotone-velocity bound + offsets)
@@ -300,8 +346,9 @@ struct LaneGame {
                 const T o = s.TR(e, k, a);
                 olo = tmin(olo, o); ohi = tmax(ohi, o);
             }
-            const T lo = p + tmin(T(0), tmin(v, vE) * trem) + olo;
-            const T hi = p + tmax(T(0), tmax(v, vE) * trem) + ohi;
+            const T env = (kNoise && e != PK) ? P.nz_env : T(0);
+            const T lo = p + tmin(T(0), tmin(v, vE) * trem) + olo - env;
+            const T hi = p + tmax(T(0), tmax(v, vE) * trem) + ohi + env;
             s.F(S::BB + 4 * e + 2 * a) = lo;
             s.F(S::BB + 4 * e + 2 * a + 1) = hi;
         }
@@ -382,6 +429,8 @@ struct LaneGame {
         const LaneGK<T> gk = tab->e[A.ty][j];
         q = fm(A.w0, gk.k, fm(A.u, P.d.dt_col * T(j), A.sp)) + axis_off(A, c);
         v = fm(A.w0, gk.g, A.u);
+        if constexpr (kNoise)
+            if (A.ty == 0) { q += A.sgn * NZ(A.e, c, A.ax); v += A.sgn * NZ(A.e, c, 2 + A.ax); }
         if (j == 0) { q = A.sp; v = A.sv; }
     }
 
@@ -394,7 +443,8 @@ struct LaneGame {
         const Axis A = axis_of(a, wk);
         const T lim = wk >= 2 ? P.lim_x[A.ty] : P.lim_y[A.ty];
         int c0 = base;
-        const bool bis = A.fl <= base;
+        const bool noisy = kNoise && A.ty == 0;   // a noisy path is neither convex nor concave: plain column scan
+        const bool bis = !noisy && A.fl <= base;
         if (bis) {  // no pending correctOverlap jump inside the range: q is convex / concave
             T q, v;
             axis_at(A, base, q, v);
@@ -433,6 +483,19 @@ struct LaneGame {
             if (over && vm > T(0)) {
                 const T tc = col_time(c - 1) + tmax(T(0), (lim - pm) / vm);
                 if (in_step(tc)) { t_out = tc; return c; }
+            }
+            if constexpr (kNoise) {
+                if (noisy) {
+                    if (c < kGrid) {
+                        T pn, vn;
+                        axis_at(A, c + 1, pn, vn);
+                        pm = p;
+                        vm = A.u + w;
+                        p = pn;
+                        w = vn - A.u;
+                    }
+                    continue;
+                }
             }
             // left the wall again on a concave arc with no pending jump: it cannot come back
             if (was_over && !over && A.fl <= c && w > T(0)) break;
@@ -482,6 +545,8 @@ struct LaneGame {
         }
         px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + ox;
         py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + oy;
+        if constexpr (kNoise)
+            if (g.ty == 0) { px += NZ(g.e, c, 0); py += NZ(g.e, c, 1); }
     }
 
     // position and velocity at column c (velocity: same arithmetic as eval())
@@ -503,6 +568,8 @@ struct LaneGame {
         py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + oy;
         vx = fm(g.wx, gk.g, g.ux);
         vy = fm(g.wy, gk.g, g.uy);
+        if constexpr (kNoise)
+            if (g.ty == 0) { px += NZ(g.e, c, 0); py += NZ(g.e, c, 1); vx += NZ(g.e, c, 2); vy += NZ(g.e, c, 3); }
     }
     // how far the relative velocity of two segments can drift from its value at any column: each body's velocity
     // moves monotonically from its segment-start value to its column-50 value
@@ -569,7 +636,7 @@ struct LaneGame {
                 }
                 ++c;
             } else {
-                c += 1 + (c < fl_ab ? 0 : free_columns(-ex, -ey, bvx - avx, bvy - avy, ssq, sigma, eps, inv_h));
+                c += 1 + ((kNoise || c < fl_ab) ? 0 : free_columns(-ex, -ey, bvx - avx, bvy - avy, ssq, sigma, eps, inv_h));
             }
         }
         return kGrid + 1;
@@ -681,7 +748,7 @@ struct LaneGame {
                 ev_add(RGS_EV_OVERLAP_FIXES);
                 ++c;
             } else {
-                c += 1 + free_columns(dx, dy, bvx - avx, bvy - avy, ssq, sigma, eps, inv_h);
+                c += 1 + (kNoise ? 0 : free_columns(dx, dy, bvx - avx, bvy - avy, ssq, sigma, eps, inv_h));
             }
         }
     }
@@ -693,6 +760,25 @@ struct LaneGame {
         const T sgn = (wk == WALL_UP || wk == WALL_RIGHT) ? T(1) : T(-1);
         const T lim = ax == 0 ? P.lim_x[A.ty] : P.lim_y[A.ty];
         const T lim_in = ax == 0 ? P.lim_x_in[A.ty] : P.lim_y_in[A.ty];
+        if constexpr (kNoise) {
+            if (A.ty == 0) {   // noisy path: every column from the closed form + noise + the offsets recorded so far
+                Axis B = A;
+#pragma unroll 1
+                for (int c = base + 1; c <= kGrid; ++c) {
+                    T p, v;
+                    axis_at(B, c, p, v);
+                    if (p >= lim) {
+                        const T f = tmin(p - P.d.wall_fix * (p - lim), lim_in) - p;
+                        record_fix(bi, c, ax == 0 ? sgn * f : T(0), ax == 0 ? T(0) : sgn * f);
+                        ev_add(RGS_EV_OVERLAP_FIXES);
+                        if (B.fl == B.cs) B.ff = c;
+                        B.fl = c;
+                        B.off_t += f;
+                    }
+                }
+                return;
+            }
+        }
         {
             T qe, ve;
             axis_at(A, kGrid, qe, ve);
@@ -721,6 +807,7 @@ struct LaneGame {
                             double *dv_sq_out = nullptr) const {
         int rj = -1;
         goal = 0;
+        if constexpr (kNoise) ++nz_epoch;   // fresh noise for everything this event re-integrates
         {
             int nb = (int)floor(since_t0(et) / P.d.dt_col) + 1;  // :237
             if (nb > kGrid) { nb = kGrid; ev_add(RGS_EV_BASE_CLAMP); }
@@ -735,6 +822,8 @@ struct LaneGame {
         const T uix = s.F(S::CMD + 2 * ei), uiy = s.F(S::CMD + 2 * ei + 1);
         advance_axis(pix, vix, uix, dt_t, P.neg_inv_tau[tyi]);
         advance_axis(piy, viy, uiy, dt_t, P.neg_inv_tau[tyi]);
+        if constexpr (kNoise)
+            if (!tyi) noise_kick(ei, 0, dt_t, pix, piy, vix, viy);
         if (ekind == PAIR) {  // :242-299
             const int tyj = (ej == PK);
             T qjx, qjy, qvjx, qvjy;
@@ -743,6 +832,8 @@ struct LaneGame {
             const T ujx = s.F(S::CMD + 2 * ej), ujy = s.F(S::CMD + 2 * ej + 1);
             advance_axis(pjx, vjx, ujx, dt_t, P.neg_inv_tau[tyj]);
             advance_axis(pjy, vjy, ujy, dt_t, P.neg_inv_tau[tyj]);
+            if constexpr (kNoise)
+                if (!tyj) noise_kick(ej, 0, dt_t, pjx, pjy, vjx, vjy);
             {  // residual overlap of the constant-velocity impact-time estimate :259-265
                 const T dx = pjx - pix, dy = pjy - piy;
                 const T ssq = dx * dx + dy * dy;
@@ -773,6 +864,10 @@ struct LaneGame {
             advance_axis(piy, viy, uiy, h_rest, P.neg_inv_tau[tyi]);
             advance_axis(pjx, vjx, ujx, h_rest, P.neg_inv_tau[tyj]);
             advance_axis(pjy, vjy, ujy, h_rest, P.neg_inv_tau[tyj]);
+            if constexpr (kNoise) {
+                if (!tyi) noise_kick(ei, 1, h_rest, pix, piy, vix, viy);
+                if (!tyj) noise_kick(ej, 1, h_rest, pjx, pjy, vjx, vjy);
+            }
             {  // correctOverlap at column base :287
                 const T dx = pjx - pix, dy = pjy - piy;
                 const T ssq = dx * dx + dy * dy;
@@ -805,6 +900,8 @@ struct LaneGame {
             } else {
                 advance_axis(pix, vix, uix, h_rest, P.neg_inv_tau[tyi]);
                 advance_axis(piy, viy, uiy, h_rest, P.neg_inv_tau[tyi]);
+                if constexpr (kNoise)
+                    if (!tyi) noise_kick(ei, 1, h_rest, pix, piy, vix, viy);
                 {  // correctOverlap(wall) at column base :334 (folded limit, kept strictly inside)
                     const bool xa = ekind >= WALL_RIGHT;
                     const T sgn = (ekind == WALL_UP || ekind == WALL_RIGHT) ? T(1) : T(-1);
@@ -836,7 +933,7 @@ struct LaneGame {
     // ~10 % fewer instructions overall (those steps were 12 % of them).
     // The snapshot's run-time-indexed words live in the lane's global scratch area behind the tracks (JF / JI),
     // not in local memory; only its scalars are registers.
-    static constexpr bool kJamFF = NT <= 3;
+    static constexpr bool kJamFF = NT <= 3 && !kNoise;   // (fresh noise every iteration: the loop state never repeats)
     struct JamSnap {
         unsigned qmask, owners, wbits, pbits, ranks;
         int base, ri, rj, scored, seq, counter, log_n;
@@ -845,8 +942,8 @@ struct LaneGame {
     // counters [17]; per logged event kind | i << 4 | (j + 1) << 8 | goal << 12 [kJamLog] and the two halves of
     // dv_sq of a player-player impact (-1: none) [2 kJamLog]
     static constexpr int JI_EV = 5 * E, JI_LOG = 5 * E + 17, JI_DV = JI_LOG + kJamLog;
-    RGS_DEV T &JF(int w) const { return s.trk[(size_t)(S::TRK_WORDS + w) * s.tstride]; }
-    RGS_DEV int &JI(int w) const { return *reinterpret_cast<int *>(&s.trk[(size_t)(S::TRK_WORDS + S::JAM_F + w) * s.tstride]); }
+    RGS_DEV T &JF(int w) const { return s.trk[(size_t)(S::JAM0 + w) * s.tstride]; }
+    RGS_DEV int &JI(int w) const { return s.G(S::JAM0 + S::JAM_F + w); }
     static RGS_DEV bool same_bits(T a, T b) {
         if constexpr (sizeof(T) == 4) {
             unsigned x, y;
@@ -883,10 +980,10 @@ struct LaneGame {
             JI(E + e) = s.I(S::FL + e);
             JI(2 * E + e) = s.I(S::QI + e) & 0xFFFF;
             JI(3 * E + e) = s.I(S::FF + e);
-            JI(4 * E + e) = s.I(S::TS + e);
+            JI(4 * E + e) = s.G(S::TS + e);
         }
 #pragma unroll 1
-        for (int k = 0; k < 17; ++k) JI(JI_EV + k) = s.I(S::EVC + k);
+        for (int k = 0; k < 17; ++k) JI(JI_EV + k) = s.G(S::EVC + k);
         J.qmask = qmask; J.owners = owners; J.wbits = wbits; J.pbits = pbits; J.ranks = queue_ranks(qmask);
         J.base = base; J.ri = ri; J.rj = rj; J.scored = scored; J.seq = seq; J.counter = counter;
         J.log_n = 0;
@@ -901,9 +998,8 @@ struct LaneGame {
             if (!same_bits(JF(w), s.F(w))) return false;
 #pragma unroll 1
         for (int e = 0; e < E; ++e) {
-            if (JI(e) != s.I(S::CS + e) || JI(E + e) != s.I(S::FL + e) || JI(3 * E + e) != s.I(S::FF + e) ||
-                JI(4 * E + e) != s.I(S::TS + e))
-                return false;
+            if (JI(e) != s.I(S::CS + e) || JI(E + e) != s.I(S::FL + e) || JI(3 * E + e) != s.I(S::FF + e)) return false;
+            if (s.I(S::FL + e) != s.I(S::FF + e) && JI(4 * E + e) != s.G(S::TS + e)) return false;
             if ((qmask >> e) & 1u)
                 if (!same_bits(JF(S::QT + e), s.F(S::QT + e)) || JI(2 * E + e) != (s.I(S::QI + e) & 0xFFFF)) return false;
         }
@@ -920,7 +1016,7 @@ struct LaneGame {
                                        RGS_EV_BASE_CLAMP, RGS_EV_OVERLAP_FIXES};
 #pragma unroll 1
         for (int k = 0; k < (int)(sizeof(kAdd) / sizeof(int)); ++k)
-            s.I(S::EVC + kAdd[k]) += m * (s.I(S::EVC + kAdd[k]) - JI(JI_EV + kAdd[k]));
+            s.G(S::EVC + kAdd[k]) += m * (s.G(S::EVC + kAdd[k]) - JI(JI_EV + kAdd[k]));
 #pragma unroll 1
         for (int r = 0; r < m; ++r)
 #pragma unroll 1
@@ -1035,6 +1131,29 @@ struct LaneGame {
         Bits<4 * E> wb;
         Bits<NPAIR> pb;
         step_head(wb, pb);
+        if constexpr (kNoise) {
+            nz_step = (unsigned)live;
+            nz_epoch = 0;
+            if (!(wb.any() || pb.any())) {
+                // nothing can touch anything even with the noise envelope: only the END of every player's noise path
+                // matters, drawn from the accumulated Gaussian of the 50 sub-steps (same distribution)
+                nz_on = false;
+                step_commit();
+#pragma unroll 1
+                for (int e = 0; e < NP; ++e) {
+                    T g[4];
+                    normals4<T>(P.seed_lo, P.seed_hi, nz_game, nz_step, (unsigned)e, g);
+                    s.F(S::SP + 4 * e) += fm(P.nz_end[1], g[0], P.nz_end[2] * g[1]);
+                    s.F(S::SP + 4 * e + 1) += fm(P.nz_end[1], g[2], P.nz_end[2] * g[3]);
+                    s.F(S::SP + 4 * e + 2) += P.nz_end[0] * g[0];
+                    s.F(S::SP + 4 * e + 3) += P.nz_end[0] * g[2];
+                }
+                return 1;
+            }
+            nz_on = true;
+#pragma unroll 1
+            for (int e = 0; e < NP; ++e) gen_noise_path(e, 0);
+        }
         const int counter = event_loop(wb, pb, sa, sb, dmg, live);
         step_commit();
         return counter;
@@ -1052,15 +1171,15 @@ struct LaneGame {
                 s.I(S::CS + e) = 0;
                 s.I(S::FL + e) = 0;
                 s.I(S::FF + e) = 0;
-                s.I(S::TS + e) = 0;
                 T lohi[4];
 #pragma unroll
                 for (int a = 0; a < 2; ++a) {
                     s.F(S::OFF + 2 * e + a) = T(0);
                     const T p = s.F(S::SP + 4 * e + a), v = s.F(S::SP + 4 * e + 2 + a), u = s.F(S::CMD + 2 * e + a);
                     const T vE = fm(v - u, gE[ty], u);
-                    lohi[2 * a] = p + tmin(T(0), tmin(v, vE) * trem) + T(0);
-                    lohi[2 * a + 1] = p + tmax(T(0), tmax(v, vE) * trem) + T(0);
+                    const T env = (kNoise && !ty) ? P.nz_env : T(0);
+                    lohi[2 * a] = p + tmin(T(0), tmin(v, vE) * trem) - env;
+                    lohi[2 * a + 1] = p + tmax(T(0), tmax(v, vE) * trem) + env;
                     s.F(S::BB + 4 * e + 2 * a) = lohi[2 * a];
                     s.F(S::BB + 4 * e + 2 * a + 1) = lohi[2 * a + 1];
                 }
@@ -1124,12 +1243,13 @@ RGS_DEV void write_traj_lane(const RunArgs &A, const LaneScratch<T, NT> &s, int6
 // kPolicy: the commands come from the on-device surrogate policy (rgs_policy.cuh), evaluated on the state at the
 // start of EVERY game-step (the reference calls the team methods once per step, py/MonteCarlo.py:37-46); a separate
 // instantiation, so that the open-loop kernels do not carry its code.
-template <typename T, int NT, bool kPolicy = false>
+template <typename T, int NT, bool kPolicy = false, bool kNoise = false>
 RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const LaneTab<T> *tab, const LaneScratch<T, NT> &s,
                                int64_t game) {
     constexpr int E = 2 * NT + 1, PK = 2 * NT, SREC = 2 + 4 * E, NP = 2 * NT;
     using S = LaneScratch<T, NT>;
-    const LaneGame<T, NT> G(P, tab, s);
+    const LaneGame<T, NT, kNoise> G(P, tab, s);
+    if constexpr (kNoise) G.nz_game = A.noise_game0 + game;
     double *srec = A.state + game * SREC;
 #pragma unroll 1
     for (int slot = 0; slot < E; ++slot) {
@@ -1149,11 +1269,11 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
     // with run-time indices), added to the game's int64 record at the end; the hash is carried over
     long long *gev = A.events + game * RGS_N_EVENTS;
 #pragma unroll 1
-    for (int i = 0; i < RGS_N_EVENTS; ++i) s.I(S::EVC + i) = 0;
+    for (int i = 0; i < RGS_N_EVENTS; ++i) s.G(S::EVC + i) = 0;
     {
         const unsigned long long h0 = (unsigned long long)gev[RGS_EV_HASH];
-        s.I(S::EVC + RGS_EV_HASH) = (int)(unsigned)h0;
-        s.I(S::EVC + 16) = (int)(unsigned)(h0 >> 32);
+        s.G(S::EVC + RGS_EV_HASH) = (int)(unsigned)h0;
+        s.G(S::EVC + 16) = (int)(unsigned)(h0 >> 32);
     }
     double *dmg = A.damage + game * (NP * NP);
     long long live = gev[RGS_EV_LIVE_STEPS], loop_iters = gev[RGS_EV_LOOP_ITERS], decided = gev[RGS_EV_DECIDED_STEP];
@@ -1210,8 +1330,8 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
         else if (i == RGS_EV_LOOP_ITERS) v = loop_iters;
         else if (i == RGS_EV_DECIDED_STEP) v = decided;
         else if (i == RGS_EV_HASH)
-            v = (long long)(((unsigned long long)(unsigned)s.I(S::EVC + 16) << 32) | (unsigned)s.I(S::EVC + RGS_EV_HASH));
-        else v = gev[i] + (long long)s.I(S::EVC + i);
+            v = (long long)(((unsigned long long)(unsigned)s.G(S::EVC + 16) << 32) | (unsigned)s.G(S::EVC + RGS_EV_HASH));
+        else v = gev[i] + (long long)s.G(S::EVC + i);
         gev[i] = v;
     }
 }

@@ -12,8 +12,10 @@
 
 namespace rgs {
 
-template <typename T, int NT, int THREADS, bool kPolicy = false>
-__global__ void __launch_bounds__(THREADS, 1) rollout_lane_kernel(const __grid_constant__ FastParams<T> P,
+template <typename T, int NT, int THREADS, bool kPolicy = false, bool kNoise = false>
+// fp32: at most 128 registers per lane, i.e. 16 resident warps per SM whatever the CTA size (the kernel is bound by
+// instruction-fetch latency, which only resident warps hide: 12 instead of 16 warps cost 40 %, profiles/r02_*)
+__global__ void __launch_bounds__(THREADS, sizeof(T) == 4 ? 512 / THREADS : 1) rollout_lane_kernel(const __grid_constant__ FastParams<T> P,
                                                                   const __grid_constant__ RunArgs A, const int lanes) {
     // `lanes` = games per CTA.  It equals THREADS except in the one-warp instantiation used for small batches
     // (launch_lane_nt), where a CTA may carry fewer games than it has threads: a latency-bound batch finishes sooner
@@ -32,11 +34,12 @@ __global__ void __launch_bounds__(THREADS, 1) rollout_lane_kernel(const __grid_c
     __syncthreads();
     if ((int)threadIdx.x >= per_cta) return;
     const size_t warp = ((size_t)blockIdx.x * THREADS + threadIdx.x) >> 5;
-    T *scr = static_cast<T *>(A.lane_scratch) + warp * ((size_t)S::SCR_WORDS * 32) + (threadIdx.x & 31);
+    constexpr size_t scr_words = kNoise ? S::SCR_WORDS_NOISE : S::SCR_WORDS;
+    T *scr = static_cast<T *>(A.lane_scratch) + warp * (scr_words * 32) + (threadIdx.x & 31);
     const S s{fw + threadIdx.x, iw + threadIdx.x, per_cta, scr, 32};
     const int64_t stride = (int64_t)gridDim.x * per_cta;
     for (int64_t game = (int64_t)blockIdx.x * per_cta + threadIdx.x; game < A.n_games; game += stride)
-        rollout_lane_game<T, NT, kPolicy>(P, A, tab, s, game);
+        rollout_lane_game<T, NT, kPolicy, kNoise>(P, A, tab, s, game);
 }
 
 template <typename T, int NT>
@@ -53,10 +56,10 @@ constexpr int lane_big_threads() { return lane_smem_bytes<T, NT>(128) <= 110 * 1
 
 constexpr int kSmallWarpsPerSm = 7;   // one-warp CTAs per SM aimed at by the small-batch path (see launch_lane_nt)
 
-template <typename T, int NT, int kThreads, bool kPolicy>
+template <typename T, int NT, int kThreads, bool kPolicy, bool kNoise>
 static cudaError_t lane_resident_ctas(int lanes, int *per_sm) {
     const size_t smem = lane_smem_bytes<T, NT>(lanes);
-    auto kern = rollout_lane_kernel<T, NT, kThreads, kPolicy>;
+    auto kern = rollout_lane_kernel<T, NT, kThreads, kPolicy, kNoise>;
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(per_sm, kern, kThreads, smem);
@@ -64,29 +67,30 @@ static cudaError_t lane_resident_ctas(int lanes, int *per_sm) {
     return err;
 }
 
-template <typename T, int NT, int kThreads, bool kPolicy = false>
+template <typename T, int NT, int kThreads, bool kPolicy = false, bool kNoise = false>
 static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count,
                                      int lanes = kThreads) {
     int per_sm = 0;
-    cudaError_t err = lane_resident_ctas<T, NT, kThreads, kPolicy>(lanes, &per_sm);
+    cudaError_t err = lane_resident_ctas<T, NT, kThreads, kPolicy, kNoise>(lanes, &per_sm);
     if (err != cudaSuccess) return err;
     int64_t blocks = (A.n_games + lanes - 1) / lanes;
     const int64_t cap = (int64_t)sm_count * per_sm;  // persistent grid: resident CTAs x SM count
     if (blocks > cap) blocks = cap;  // (equalising the rounds per lane was measured: no gain, profiles/r01_ab_variants.md)
     if (blocks < 1) blocks = 1;
-    const size_t need = (size_t)blocks * kThreads * LaneScratch<T, NT>::SCR_WORDS * sizeof(T);
+    const size_t words = kNoise ? LaneScratch<T, NT>::SCR_WORDS_NOISE : LaneScratch<T, NT>::SCR_WORDS;
+    const size_t need = (size_t)blocks * kThreads * words * sizeof(T);
     if (!A.lane_scratch || A.lane_scratch_bytes < need) return cudaErrorInvalidValue;
-    rollout_lane_kernel<T, NT, kThreads, kPolicy><<<(unsigned)blocks, kThreads, lane_smem_bytes<T, NT>(lanes), stream>>>(P, A, lanes);
+    rollout_lane_kernel<T, NT, kThreads, kPolicy, kNoise><<<(unsigned)blocks, kThreads, lane_smem_bytes<T, NT>(lanes), stream>>>(P, A, lanes);
     return cudaGetLastError();
 }
 
 // Batches smaller than one big CTA per SM (the K3 sampler's 4096 candidates) use one-warp CTAs carrying only a few
 // games each, so that they spread over all SMs.
-template <typename T, int NT>
+template <typename T, int NT, bool kNoise>
 static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count) {
     constexpr int kBig = lane_big_threads<T, NT>();
     if (A.synth == 2) {  // closed loop on the on-device policy: instantiated for the reference's 2v2 only
-        if constexpr (NT == 2) return launch_lane_sized<T, NT, kBig, true>(P, A, stream, sm_count);
+        if constexpr (NT == 2) return launch_lane_sized<T, NT, kBig, true, kNoise>(P, A, stream, sm_count);
         else return cudaErrorNotSupported;
     }
     if (A.n_games < (int64_t)sm_count * kBig) {
@@ -96,27 +100,28 @@ static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cuda
         int lanes = (int)((A.n_games + (int64_t)sm_count * kSmallWarpsPerSm - 1) / ((int64_t)sm_count * kSmallWarpsPerSm));
         if (lanes < 1) lanes = 1;
         if (lanes > 32) lanes = 32;
-        return launch_lane_sized<T, NT, 32>(P, A, stream, sm_count, lanes);
+        return launch_lane_sized<T, NT, 32, false, kNoise>(P, A, stream, sm_count, lanes);
     }
-    return launch_lane_sized<T, NT, kBig>(P, A, stream, sm_count);
+    return launch_lane_sized<T, NT, kBig, false, kNoise>(P, A, stream, sm_count);
 }
 
 // upper bound of the scratch any launch of this (T, NT) can need on a device with sm_count SMs
-template <typename T, int NT>
+template <typename T, int NT, bool kNoise>
 static cudaError_t lane_scratch_nt(int sm_count, size_t *bytes) {
     constexpr int kBig = lane_big_threads<T, NT>();
     int per_sm = 0;
-    cudaError_t err = lane_resident_ctas<T, NT, kBig, false>(kBig, &per_sm);
+    cudaError_t err = lane_resident_ctas<T, NT, kBig, false, kNoise>(kBig, &per_sm);
     if (err != cudaSuccess) return err;
     int64_t threads = (int64_t)per_sm * kBig;
     if constexpr (NT == 2) {
-        err = lane_resident_ctas<T, NT, kBig, true>(kBig, &per_sm);
+        err = lane_resident_ctas<T, NT, kBig, true, kNoise>(kBig, &per_sm);
         if (err != cudaSuccess) return err;
         if ((int64_t)per_sm * kBig > threads) threads = (int64_t)per_sm * kBig;
     }
     // small-batch path: at most kSmallWarpsPerSm (+1 for the rounding of games per CTA) one-warp CTAs per SM
     if ((int64_t)(kSmallWarpsPerSm + 1) * 32 > threads) threads = (int64_t)(kSmallWarpsPerSm + 1) * 32;
-    *bytes = (size_t)sm_count * (size_t)threads * LaneScratch<T, NT>::SCR_WORDS * sizeof(T);
+    const size_t words = kNoise ? LaneScratch<T, NT>::SCR_WORDS_NOISE : LaneScratch<T, NT>::SCR_WORDS;
+    *bytes = (size_t)sm_count * (size_t)threads * words * sizeof(T);
     return cudaSuccess;
 }
 
@@ -134,17 +139,27 @@ static cudaError_t by_team(int n_team, F &&f) {
     }
 }
 
+// process noise (rgs_params.noise != 0) selects the kNoise instantiations, so that the noise-free kernels do not carry
+// the generator's code
 cudaError_t launch_rollout_lane_f32(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count) {
     const FastParams<float> P = make_fast_params<float>(p);
-    return by_team<float>(n_team, [&](auto nt) { return launch_lane_nt<float, decltype(nt)::value>(P, A, stream, sm_count); });
+    if (p.noise != 0.0)
+        return by_team<float>(n_team, [&](auto nt) { return launch_lane_nt<float, decltype(nt)::value, true>(P, A, stream, sm_count); });
+    return by_team<float>(n_team, [&](auto nt) { return launch_lane_nt<float, decltype(nt)::value, false>(P, A, stream, sm_count); });
 }
 cudaError_t launch_rollout_lane_f64(int n_team, const rgs_params &p, const RunArgs &A, cudaStream_t stream, int sm_count) {
     const FastParams<double> P = make_fast_params<double>(p);
-    return by_team<double>(n_team, [&](auto nt) { return launch_lane_nt<double, decltype(nt)::value>(P, A, stream, sm_count); });
+    if (p.noise != 0.0)
+        return by_team<double>(n_team, [&](auto nt) { return launch_lane_nt<double, decltype(nt)::value, true>(P, A, stream, sm_count); });
+    return by_team<double>(n_team, [&](auto nt) { return launch_lane_nt<double, decltype(nt)::value, false>(P, A, stream, sm_count); });
 }
-cudaError_t lane_scratch_bytes(int n_team, int fp64, int sm_count, size_t *bytes) {
-    if (fp64) return by_team<double>(n_team, [&](auto nt) { return lane_scratch_nt<double, decltype(nt)::value>(sm_count, bytes); });
-    return by_team<float>(n_team, [&](auto nt) { return lane_scratch_nt<float, decltype(nt)::value>(sm_count, bytes); });
+cudaError_t lane_scratch_bytes(int n_team, int fp64, int noise, int sm_count, size_t *bytes) {
+    if (fp64) {
+        if (noise) return by_team<double>(n_team, [&](auto nt) { return lane_scratch_nt<double, decltype(nt)::value, true>(sm_count, bytes); });
+        return by_team<double>(n_team, [&](auto nt) { return lane_scratch_nt<double, decltype(nt)::value, false>(sm_count, bytes); });
+    }
+    if (noise) return by_team<float>(n_team, [&](auto nt) { return lane_scratch_nt<float, decltype(nt)::value, true>(sm_count, bytes); });
+    return by_team<float>(n_team, [&](auto nt) { return lane_scratch_nt<float, decltype(nt)::value, false>(sm_count, bytes); });
 }
 
 }  // namespace rgs

@@ -99,7 +99,11 @@ class BatchedGameSim:
     "fast64" (K2 in fp64).  Keyword parameters are those of GameSim::reset plus the constructor
     constants (arena_x, arena_y, player_radius, puck_radius, goal_height)."""
 
-    def __init__(self, n_games, device=None, mode="exact", players_per_team=2, **params):
+    def __init__(self, n_games, device=None, mode="exact", players_per_team=2, first_game=0, **params):
+        """params: the fields of rgs_params (dt, winning_score, noise, seed, tau_puck, tau_player, player_mass,
+        puck_mass, arena_x, arena_y, player_radius, puck_radius, goal_height).  noise > 0 (process noise on the
+        player accelerations, reference src/GameSim.cpp:62-68) runs in the "fast" / "fast64" modes; its streams are
+        keyed by (seed, first_game + g), so a batch sharded over GPUs draws what the unsharded batch draws."""
         import torch  # tensor hand-off only
 
         self._torch = torch
@@ -117,7 +121,7 @@ class BatchedGameSim:
         p.mode = _MODES[mode]
         p.players_per_team = self.n_team
         for k, v in params.items():
-            if not hasattr(p, k) or k in ("mode", "players_per_team", "reserved"):
+            if not hasattr(p, k) or k in ("mode", "players_per_team"):
                 raise TypeError(f"unknown parameter {k!r}")
             setattr(p, k, v)
         self.params = p
@@ -125,6 +129,8 @@ class BatchedGameSim:
         self.action_dtype = torch.float32 if p.mode == _capi.MODE_FAST_F32 else torch.float64
         self._h = C.c_void_p()
         _capi.check(self._lib.rgs_batch_create(C.byref(self._h), self.device.index or 0, self.n_games, C.byref(p)))
+        if first_game:
+            self.set_game_offset(first_game)
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -146,9 +152,13 @@ class BatchedGameSim:
             t = t.to(dtype)
         return t.contiguous()
 
+    def set_game_offset(self, first_game):
+        """Global index of game 0 of this batch (keys the per-game process-noise streams)."""
+        _capi.check(self._lib.rgs_batch_set_game_offset(self._h, int(first_game)))
+
     def set_params(self, **params):
         for k, v in params.items():
-            if not hasattr(self.params, k) or k in ("mode", "players_per_team", "reserved"):
+            if not hasattr(self.params, k) or k in ("mode", "players_per_team"):
                 raise TypeError(f"unknown parameter {k!r}")
             setattr(self.params, k, v)
         _capi.check(self._lib.rgs_batch_set_params(self._h, C.byref(self.params)))

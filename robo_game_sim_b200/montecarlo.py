@@ -99,9 +99,11 @@ def monte_carlo_batched(mc_params, actions=None, policy=None, *, mode="fast", ra
     if rank == 0 and getattr(mc_params, "log_prefix", None):
         write_configuration(mc_params, mc_params.log_prefix)
 
-    sim = BatchedGameSim(count, device=device, mode=mode, dt=mc_params.dt, winning_score=int(mc_params.winning_score),
-                         noise=mc_params.noise_stdev, tau_puck=mc_params.tau_puck, tau_player=mc_params.tau_player,
-                         player_mass=mc_params.player_mass, puck_mass=mc_params.puck_mass)
+    if mc_params.noise_stdev and mode == "exact":
+        mode = "fast64"   # process noise runs in the K2 formulation (statistical parity; see rgs_params.noise)
+    sim = BatchedGameSim(count, device=device, mode=mode, first_game=first + 1, dt=mc_params.dt,
+                         winning_score=int(mc_params.winning_score), noise=mc_params.noise_stdev, tau_puck=mc_params.tau_puck,
+                         tau_player=mc_params.tau_player, player_mass=mc_params.player_mass, puck_mass=mc_params.puck_mass)
     lib = _capi.load()
     if randomize:
         x0 = torch.empty((count, 4), dtype=torch.float64, device=sim.device)
@@ -228,7 +230,9 @@ def monte_carlo(mc_params, team_A_run_method, team_B_run_method, cbf_run_method=
 
     first, count = shard_range(num_runs, rank, world_size)
     mode = mode or ("fast" if on_device else "exact")
-    sim = BatchedGameSim(count, device=device, mode=mode, **common)
+    if mc_params.noise_stdev and mode == "exact":
+        mode = "fast64"   # process noise runs in the K2 formulation (statistical parity; see rgs_params.noise)
+    sim = BatchedGameSim(count, device=device, mode=mode, first_game=first + 1, **common)   # run i <-> game index i
     sim.reset(x0_ball=np.asarray(mc_params.x0_ball, dtype=np.float64))
     zero = torch.zeros((1, 4, 2), dtype=sim.action_dtype, device=sim.device)
     live = torch.zeros(count, dtype=torch.int64, device=sim.device)

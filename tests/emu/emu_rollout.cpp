@@ -23,7 +23,7 @@ void run_exact(const rgs_params &p, const rgs::RunArgs &A) {
     emu::run_warp([&](int lane) { rgs::rollout_exact_warp<NT>(P, A, W.get(), lane, 0, 1); });
 }
 
-template <typename T, int NT>
+template <typename T, int NT, bool kNoise = false>
 void run_lane(const rgs_params &p, const rgs::RunArgs &A) {
     using S = rgs::LaneScratch<T, NT>;
     auto tab = std::make_unique<rgs::LaneTab<T>>();
@@ -32,20 +32,20 @@ void run_lane(const rgs_params &p, const rgs::RunArgs &A) {
         for (int i = 0; i < rgs::kCols; ++i) { tab->e[ty][i].g = P.tab_g[ty][i]; tab->e[ty][i].k = P.tab_k[ty][i]; }
     T fw[S::NF];
     int iw[S::NI];
-    std::vector<T> scr(S::SCR_WORDS);   // the lane's global scratch area (correctOverlap tracks + jam snapshot)
+    std::vector<T> scr(S::SCR_WORDS_NOISE);   // the lane's global scratch area (tracks, event counters, jam snapshot, noise)
     S s{fw, iw, 1, scr.data(), 1};
     if (A.synth == 2) {   // closed loop on the on-device surrogate policy (instantiated for 2v2, like the library)
         if constexpr (NT == 2)
-            for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT, true>(P, A, tab.get(), s, g);
-    } else for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT>(P, A, tab.get(), s, g);
+            for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT, true, kNoise>(P, A, tab.get(), s, g);
+    } else for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT, false, kNoise>(P, A, tab.get(), s, g);
 }
 
 template <int NT>
 void dispatch(const rgs_params &p, const rgs::RunArgs &A) {
     // the FAST modes run the lane body, as librgs_b200.so does
     if (p.mode == RGS_MODE_EXACT_F64) run_exact<NT>(p, A);
-    else if (p.mode == RGS_MODE_FAST_F32) run_lane<float, NT>(p, A);
-    else run_lane<double, NT>(p, A);
+    else if (p.mode == RGS_MODE_FAST_F32) { if (p.noise != 0.0) run_lane<float, NT, true>(p, A); else run_lane<float, NT>(p, A); }
+    else { if (p.noise != 0.0) run_lane<double, NT, true>(p, A); else run_lane<double, NT>(p, A); }
 }
 
 }  // namespace
@@ -82,6 +82,7 @@ extern "C" int emu_rollout(const rgs_params *p, int64_t n_games, double *state, 
     A.synth = synth;
     A.seed = seed;
     A.first_game = first_game;
+    A.noise_game0 = first_game;
     A.step0 = step0;
     A.u_max = u_max;
     if (synth == 2) {

@@ -37,7 +37,7 @@ class RgsParams(C.Structure):
                 ("noise", C.c_double), ("tau_puck", C.c_double), ("tau_player", C.c_double),
                 ("player_mass", C.c_double), ("puck_mass", C.c_double), ("arena_x", C.c_double),
                 ("arena_y", C.c_double), ("player_radius", C.c_double), ("puck_radius", C.c_double),
-                ("goal_height", C.c_double), ("mode", C.c_int32), ("reserved", C.c_int32)]
+                ("goal_height", C.c_double), ("mode", C.c_int32), ("seed", C.c_int32)]
 
 
 class RgsPolicy(C.Structure):
@@ -130,10 +130,28 @@ def emu_lib():
     return _cache["emu"]
 
 
+def pybind_module():
+    """The pybind11 module of INTEGRATION.md section B (robo_game_sim_b200/pybind/RoboGamePyB200.cpp), built on demand
+    against the in-tree librgs_b200.so and loaded WITHOUT registering it as `robo_game_py` in sys.modules (the
+    repository's own ctypes package has that name)."""
+    if "pyb" not in _cache:
+        import glob
+        import importlib.util
+
+        d = os.path.join(ROOT, "robo_game_sim_b200", "pybind")
+        _make(d)
+        path = glob.glob(os.path.join(d, "robo_game_py*.so"))[0]
+        spec = importlib.util.spec_from_file_location("robo_game_py", path)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        _cache["pyb"] = mod
+    return _cache["pyb"]
+
+
 def default_params(n_team=2, winning_score=3, mode=MODE_EXACT_F64, **kw):
     d = dict(dt=0.05, winning_score=winning_score, players_per_team=n_team, noise=0.0, tau_puck=0.1, tau_player=0.5,
              player_mass=1.0, puck_mass=0.5, arena_x=10.0, arena_y=5.0, player_radius=0.2, puck_radius=0.175,
-             goal_height=1.0, mode=mode, reserved=0)
+             goal_height=1.0, mode=mode, seed=0)
     d.update(kw)
     return d
 
@@ -212,7 +230,7 @@ def emu_policy_commands(pd, pol, state):
 
 
 def emu_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, events=None, log_stride=0, synth=None,
-                policy=None):
+                policy=None, first_game=0):
     """The product's kernel body stepped on the CPU warp emulator (one warp, games in sequence).
     policy: a default_policy() dict = closed loop on the on-device surrogate policy (actions ignored)."""
     lib = emu_lib()
@@ -243,6 +261,40 @@ def emu_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, events
         stride = 0 if shared else n_act * 4 * nt
         rc = lib.emu_rollout(C.byref(p), n, _ptr(state), _ptr(t), _ptr(damage), _ptr(events, C.c_int64),
                              actions.ctypes.data_as(C.c_void_p), n_act, hold, stride, n_steps, log_stride, _ptr(traj),
-                             0, 0, 0, 0, 0.0)
+                             0, 0, first_game, 0, 0.0)
     assert rc == 0
     return dict(state=state, t=t, damage=damage, events=events, traj=traj)
+
+
+# ---- process-noise statistics against the fixture tests/golden/noise_stats.npz (reference run with noise > 0) ----
+def noise_fixture():
+    return np.load(os.path.join(ROOT, "tests", "golden", "noise_stats.npz"))
+
+
+def check_noise_moments(mean, var, n, ref_mean, ref_var, n_ref, cols, var_tol, what):
+    """Sample means within 4.5 combined standard errors (+1e-6 for the affine-vs-RK4 rounding), sample variances within
+    var_tol of each other (the ratio of two sample variances of ~Gaussian data has sd sqrt(2/n + 2/n_ref))."""
+    m, v, rm, rv = mean[..., cols], var[..., cols], ref_mean[..., cols], ref_var[..., cols]
+    z = np.abs(m - rm) / (np.sqrt(v / n + rv / n_ref) + 1e-6)
+    assert z.max() < 4.5, (what, "mean", float(z.max()))
+    live = rv > 1e-12
+    ratio = v[live] / rv[live]
+    assert ratio.min() > 1 - var_tol and ratio.max() < 1 + var_tol, (what, "variance ratio", float(ratio.min()), float(ratio.max()))
+
+
+def analytic_noise_var(noise, steps, dt=0.05, tau=0.5):
+    """(var v, var p, cov) of the accumulated process noise of a player axis after `steps` game-steps: the per-sub-step
+    increment of reference src/GameSim.cpp:62-88 (four independent stage draws) pushed through S' = M S M^T + Q."""
+    h = dt / 50
+    z = -h / tau
+    c = [1 + z + z * z / 2 + z ** 3 / 4, 2 + z + z * z / 2, 2 + z, 1.0]
+    d = [1 + z / 2 + z * z / 4, 1 + z / 2, 1.0]
+    qvv = (h / 6) ** 2 * sum(x * x for x in c)
+    qpp = (h * h / 6) ** 2 * sum(x * x for x in d)
+    qpv = (h / 6) * (h * h / 6) * sum(a * b for a, b in zip(c, d))
+    q = 1 + z / 2 + z * z / 6 + z ** 3 / 24
+    R, a = 1 + z * q, h * q
+    svv = spv = spp = 0.0
+    for _ in range(50 * steps):
+        svv, spv, spp = R * R * svv + qvv, R * (a * svv + spv) + qpv, a * a * svv + 2 * a * spv + spp + qpp
+    return noise ** 2 * svv, noise ** 2 * spp, noise ** 2 * spv

@@ -59,8 +59,12 @@ def test_argument_errors_do_not_need_a_gpu(capi):
     assert lib.rgs_batch_create(C.byref(h), 0, 4, C.byref(p)) == capi.RGS_EINVAL
     assert "players_per_team" in capi.last_error()
     p = capi.default_params()
-    p.noise = 0.1
+    p.noise = 0.1                       # process noise: FAST modes only (statistical parity), never the exact mode
     assert lib.rgs_batch_create(C.byref(h), 0, 4, C.byref(p)) == capi.RGS_EUNSUPPORTED
+    assert "FAST" in capi.last_error()
+    p.noise = -1.0
+    p.mode = capi.MODE_FAST_F32
+    assert lib.rgs_batch_create(C.byref(h), 0, 4, C.byref(p)) == capi.RGS_EINVAL
     p = capi.default_params()
     p.mode = 7
     assert lib.rgs_batch_create(C.byref(h), 0, 4, C.byref(p)) == capi.RGS_EINVAL
@@ -219,3 +223,25 @@ def test_sampler_targets_follow_the_reference_play_logic():
     assert a.shape == (16, 5, 4, 2) and a.dtype == np.float32
     assert np.all(a[0] == 0) and np.all(a[:, :, 2:] == 0) and np.abs(a[1:, :, :2]).max() <= 10.0 and a[1:, :, :2].std() > 3
     assert np.array_equal(a, sp.candidate_actions(16, 5, players=(0, 1), seed=3))
+
+
+def test_pybind11_translation_unit_builds_and_binds():
+    """INTEGRATION.md section B is a real file (robo_game_sim_b200/pybind/RoboGamePyB200.cpp): it compiles against
+    pybind11 + include/rgs_capi.h, links librgs_b200.so, and exposes the reference's surface
+    (src/RoboGamePy.cpp:15-24): GameSim {__init__, reset, undecided, run, __repr__}, reset with the 5 trailing
+    defaults.  Without a GPU the constructor fails loudly (no CPU path)."""
+    import inspect
+
+    m = tl.pybind_module()
+    assert m.__name__ == "robo_game_py"
+    for name in ("reset", "undecided", "run", "__repr__", "__init__"):
+        assert hasattr(m.GameSim, name)
+    doc = m.GameSim.reset.__doc__
+    for frag in ("seed", "= 0", "tau_puck", "= 0.1", "tau_player", "= 0.5", "player_mass", "= 1.0", "puck_mass"):
+        assert frag in doc
+    assert inspect.isclass(m.GameSim)
+    import torch
+
+    if not torch.cuda.is_available():
+        with pytest.raises(RuntimeError, match="no CPU path"):
+            m.GameSim()

@@ -151,3 +151,58 @@ def test_fast_kernel_goal_and_freeze(golden):
         assert e["t"][0] == pytest.approx(0.25)
 
 
+
+
+# ---- process noise (reference src/GameSim.cpp:62-68): K2's Philox / exact-increment noise mode vs the reference ----
+PLAYER_COLS = list(range(6, 22))
+
+
+@pytest.mark.parametrize("mode", [tl.MODE_FAST_F64, tl.MODE_FAST_F32])
+def test_noise_mode_matches_reference_statistics(mode):
+    """Statistical parity of the noise mode (bitwise is a non-goal: the reference's normal stream is libstdc++'s):
+    per-step means and variances of every player's state over the runs against the fixture generated from the
+    reference with noise > 0 (tests/golden/make_noise_stats.py) -- free flight (quiet steps: the accumulated 2-D
+    Gaussian), players pressed into walls (flagged steps: full noise paths, wall marches) and contact-rich S0 games --
+    and against the analytic accumulated covariance."""
+    fx = tl.noise_fixture()
+
+    def emu(n, x0, acts, steps, hold, noise, ws=1 << 30, log=1):
+        pd = tl.default_params(winning_score=ws, noise=noise, mode=mode, seed=3)
+        x0 = np.tile(x0, (n, 1)) if x0.ndim == 1 else x0
+        a = np.tile(acts, (n, 1, 1, 1)) if acts.ndim == 3 else acts
+        return tl.emu_rollout(pd, tl.oracle_reset(pd, x0), a, steps, hold, log_stride=log)
+
+    n = 1500
+    steps, noise = int(fx["free_steps"]), float(fx["free_noise"])
+    tr = emu(n, np.zeros(4), fx["free_actions"], steps, steps, noise)["traj"][:, :, 1:23]
+    tl.check_noise_moments(tr.mean(0), tr.var(0, ddof=1), n, fx["free_mean"], fx["free_var"], int(fx["free_n"]), PLAYER_COLS, 0.2, "free")
+    vv, pp, _ = tl.analytic_noise_var(noise, steps)
+    assert abs(tr[:, -1, 8].var(ddof=1) / vv - 1) < 0.2 and abs(tr[:, -1, 6].var(ddof=1) / pp - 1) < 0.2
+    assert np.all(tr[:, :, 2:6] == 0.0)            # the puck has no process noise (f_puck, :90-96)
+    steps, noise, every = int(fx["press_steps"]), float(fx["press_noise"]), int(fx["press_every"])
+    e = emu(n, np.zeros(4), fx["press_actions"], steps, steps, noise, log=every)
+    tr = e["traj"][:, :, 1:23]
+    tl.check_noise_moments(tr.mean(0), tr.var(0, ddof=1), n, fx["press_mean"], fx["press_var"], int(fx["press_n"]), PLAYER_COLS[:12], 0.25, "press")
+    assert e["events"][:, tl.EV["WALL_UP"]].min() >= 1
+    n, steps, hold = 2000, int(fx["s0_steps"]), int(fx["s0_hold"])
+    x0, a = tl.synth_inputs(int(fx["s0_seed"]), 0, n, 2, steps // hold)
+    st = emu(n, x0, a, steps, hold, float(fx["s0_noise"]), ws=1, log=0)["state"]
+    tl.check_noise_moments(st[:, 2:].mean(0), st[:, 2:].var(0, ddof=1), n, fx["s0_mean"], fx["s0_var"], int(fx["s0_n"]), list(range(4, 20)), 0.2, "s0")
+    # (the puck's final state is a mixture -- reset to 0 and frozen after a goal -- so only the players' moments are held)
+    goals, ref_goals = st[:, :2].sum(), (int(fx["s0_goals_a"]) + int(fx["s0_goals_b"])) * n / int(fx["s0_n"])
+    assert abs(goals - ref_goals) < 4.5 * np.sqrt(goals + ref_goals + 1)
+
+
+def test_noise_streams_are_keyed_by_seed_and_global_game():
+    """Same (seed, global game index) -> the same game, whatever batch it is in; another seed -> another game;
+    noise = 0 -> the noise-free kernel's bits."""
+    pd = tl.default_params(winning_score=3, noise=3.0, mode=tl.MODE_FAST_F64, seed=11)
+    x0, a = tl.synth_inputs(4, 0, 12, 2, 4)
+    s0 = tl.oracle_reset(pd, x0)
+    full = tl.emu_rollout(pd, s0, a, 40, 10)
+    part = tl.emu_rollout(pd, s0[5:9], a[5:9], 40, 10, first_game=5)
+    assert np.array_equal(full["state"][5:9], part["state"]) and np.array_equal(full["events"][5:9], part["events"])
+    other = tl.emu_rollout(dict(pd, seed=12), s0, a, 40, 10)
+    assert not np.array_equal(full["state"], other["state"])
+    quiet = tl.emu_rollout(dict(pd, noise=0.0), s0, a, 40, 10)
+    assert np.abs(quiet["state"] - full["state"]).max() > 1e-6
