@@ -41,6 +41,7 @@ template <typename T>
 struct DevParams {
     T dt, dt_col, dt_col_h2, dt_col_h6;
     T tau[2], drag[2], mass[2], rad[2];
+    T inv_tau[2];    // RN(1 / tau): the reciprocal K1's division by tau is built from (rgs_exact.cuh div_tau); 0 = use '/' 
     T half_x, half_y, half_goal;
     T lim_hi_y[2], lim_lo_y[2], lim_hi_x[2], lim_lo_x[2];  // arena/2 - r ; -arena/2 + r
     T sig[2][2];     // r_a + r_b

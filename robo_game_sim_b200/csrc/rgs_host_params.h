@@ -42,6 +42,8 @@ inline DevParams<T> make_dev_params(const rgs_params &p) {
     d.half_goal = T(p.goal_height / 2.0);
     for (int a = 0; a < 2; ++a) {
         d.tau[a] = T(tau[a]);
+        // the reciprocal form of x / tau is exact for binary64 operands away from the exponent limits
+        d.inv_tau[a] = (tau[a] >= 0x1p-20 && tau[a] <= 0x1p20) ? T(1.0 / tau[a]) : T(0);
         d.drag[a] = T(drag[a]);
         d.mass[a] = T(mass[a]);
         d.rad[a] = T(rad[a]);
@@ -111,6 +113,7 @@ inline FastParams<T> make_fast_params(const rgs_params &p) {
         f.nz_sub[0] = T(sg * q.l11); f.nz_sub[1] = T(sg * q.l21); f.nz_sub[2] = T(sg * q.l22);
         f.nz_end[0] = T(sg * e11); f.nz_end[1] = T(sg * e21); f.nz_end[2] = T(sg * e22);
         f.nz_env = T(6.5 * std::fabs(sg) * std::sqrt(Spp));
+        f.dt_col64 = p.dt / RGS_GRID_POINTS;
         f.seed_lo = (uint32_t)p.seed;
         f.seed_hi = 0x5EEDu;
     }

@@ -202,6 +202,7 @@ struct LaneGame {
     // for contacts resting on a grid time the rounding of t_ decides between two columns.
     static constexpr bool kAbsClock = sizeof(T) == 8;
     mutable T t0 = T(0);
+    mutable double tclk = 0.0;   // the game clock t_ at the start of the step (fp64, t_ += dt_ like the reference)
     RGS_DEV T col_time(int c) const {
         if constexpr (kAbsClock) return t0 + P.d.dt_col * T(c);
         else return P.d.dt_col * T(c);
@@ -281,15 +282,22 @@ struct LaneGame {
         s.I(S::FL + e) = c;
     }
 
-    // event record of the launch: counters in the scratch record, flushed to the game's int64 record at the end
-    RGS_DEV void ev_add(int k, int n = 1) const { s.G(S::EVC + k) += n; }
+    // event record of the launch: 32-bit counters (RGS_EV_* order; [RGS_EV_HASH], [16] = hash lo, hi), added to the game's
+    // int64 record at the end
+#ifdef RGS_AB_EVLOCAL
+    mutable int *evp = nullptr;
+    RGS_DEV int &EVW(int k) const { return evp[k]; }
+#else
+    RGS_DEV int &EVW(int k) const { return s.G(S::EVC + k); }
+#endif
+    RGS_DEV void ev_add(int k, int n = 1) const { EVW(k) += n; }
     RGS_DEV void hash_ev(long long live, int kind, int i, int j, int goal) const {
-        unsigned long long h = ((unsigned long long)(unsigned)s.G(S::EVC + 16) << 32) | (unsigned)s.G(S::EVC + RGS_EV_HASH);
+        unsigned long long h = ((unsigned long long)(unsigned)EVW(16) << 32) | (unsigned)EVW(RGS_EV_HASH);
         h ^= ((unsigned long long)live << 16) | ((unsigned long long)kind << 12) | ((unsigned long long)i << 8) |
              ((unsigned long long)(j < 0 ? 15 : j) << 4) | (unsigned long long)goal;   // == hash_event() of rgs_device.cuh
         h *= 0x100000001B3ULL;
-        s.G(S::EVC + RGS_EV_HASH) = (int)(unsigned)h;
-        s.G(S::EVC + 16) = (int)(unsigned)(h >> 32);
+        EVW(RGS_EV_HASH) = (int)(unsigned)h;
+        EVW(16) = (int)(unsigned)(h >> 32);
     }
 
     // state of body e at column c >= CS[e]-1 (position includes the correctOverlap offsets)
@@ -692,7 +700,7 @@ struct LaneGame {
         ++seq;
     }
     // earliest time; among equal times the most recently inserted (stable insertion sort, a11)
-    RGS_DEV void pop(unsigned &qmask, int &ei, int &ej, int &ekind, T &et) const {
+    RGS_DEV void pop(unsigned &qmask, int &ei, int &ej, int &ekind, T &et, int &ecol) const {
         int best = -1, binfo = 0;
         T bt = T(0);
 #pragma unroll 1
@@ -705,6 +713,7 @@ struct LaneGame {
         ei = best;
         et = bt;
         ekind = (binfo >> 4) & 15;
+        ecol = (binfo >> 8) & 255;
         ej = binfo & 15;
         if (ej == 15) ej = -1;
         qmask &= ~(1u << best);
@@ -803,17 +812,29 @@ struct LaneGame {
     // ---- execute one popped event (carryOutFirstCollision :237-345): advance the bodies to the time of
     // impact, resolve, start their new segments at column `base`, correctOverlap on the later columns.
     // Returns the second body to re-scan (-1 for a wall event); goal = 1 (team A) / 2 (team B) / 0.
-    RGS_DEV_BIG int resolve(int ei, int ej, int ekind, T et, int &base, int &goal, double *dmg, long long live,
+    RGS_DEV_BIG int resolve(int ei, int ej, int ekind, T et, int ecol, int &base, int &goal, double *dmg, long long live,
                             double *dv_sq_out = nullptr) const {
         int rj = -1;
         goal = 0;
         if constexpr (kNoise) ++nz_epoch;   // fresh noise for everything this event re-integrates
-        {
+        T dt_t;
+        if constexpr (kAbsClock) {
             int nb = (int)floor(since_t0(et) / P.d.dt_col) + 1;  // :237
             if (nb > kGrid) { nb = kGrid; ev_add(RGS_EV_BASE_CLAMP); }
             if (nb > base) base = nb;  // event times never run backwards by more than a rounding
+            dt_t = et - col_time(base - 1);  // :254 / :308
+        } else {
+            // The reference forms t_col = (t_ + dt_col_ (i-1)) + tau on its absolute fp64 clock (:201, :389) and takes
+            // base_idx = floor((t_col - t_) / dt_col_) + 1 (:237): for a RESTING contact (tau = 0) the rounding of t_
+            // decides between column i-1 and i, which sets how long a jammed event loop runs.  fp32 event times are
+            // step-relative; that one decision (and dt_t, :254) is taken in fp64 exactly as the reference takes it.
+            const T tau = et - col_time(ecol - 1);
+            const double tcol = (tclk + P.dt_col64 * (double)(ecol - 1)) + (double)tau;
+            int nb = (int)floor((tcol - tclk) / P.dt_col64) + 1;
+            if (nb > kGrid) { nb = kGrid; ev_add(RGS_EV_BASE_CLAMP); }
+            if (nb > base) base = nb;
+            dt_t = (T)(tcol - (tclk + P.dt_col64 * (double)(base - 1)));
         }
-        const T dt_t = et - col_time(base - 1);  // :254 / :308
         const T h_rest = P.d.dt_col - dt_t;
         const int tyi = (ei == PK);
         T qix, qiy, qvix, qviy;
@@ -933,7 +954,11 @@ struct LaneGame {
     // ~10 % fewer instructions overall (those steps were 12 % of them).
     // The snapshot's run-time-indexed words live in the lane's global scratch area behind the tracks (JF / JI),
     // not in local memory; only its scalars are registers.
-    static constexpr bool kJamFF = NT <= 3 && !kNoise;   // (fresh noise every iteration: the loop state never repeats)
+#ifdef RGS_AB_NOJAM
+    static constexpr bool kJamFF = false;
+#else
+    static constexpr bool kJamFF = NT <= 3 && !kNoise;
+#endif   // (fresh noise every iteration: the loop state never repeats)
     struct JamSnap {
         unsigned qmask, owners, wbits, pbits, ranks;
         int base, ri, rj, scored, seq, counter, log_n;
@@ -983,7 +1008,7 @@ struct LaneGame {
             JI(4 * E + e) = s.G(S::TS + e);
         }
 #pragma unroll 1
-        for (int k = 0; k < 17; ++k) JI(JI_EV + k) = s.G(S::EVC + k);
+        for (int k = 0; k < 17; ++k) JI(JI_EV + k) = EVW(k);
         J.qmask = qmask; J.owners = owners; J.wbits = wbits; J.pbits = pbits; J.ranks = queue_ranks(qmask);
         J.base = base; J.ri = ri; J.rj = rj; J.scored = scored; J.seq = seq; J.counter = counter;
         J.log_n = 0;
@@ -1016,7 +1041,7 @@ struct LaneGame {
                                        RGS_EV_BASE_CLAMP, RGS_EV_OVERLAP_FIXES};
 #pragma unroll 1
         for (int k = 0; k < (int)(sizeof(kAdd) / sizeof(int)); ++k)
-            s.G(S::EVC + kAdd[k]) += m * (s.G(S::EVC + kAdd[k]) - JI(JI_EV + kAdd[k]));
+            EVW(kAdd[k]) += m * (EVW(kAdd[k]) - JI(JI_EV + kAdd[k]));
 #pragma unroll 1
         for (int r = 0; r < m; ++r)
 #pragma unroll 1
@@ -1086,9 +1111,9 @@ struct LaneGame {
                     if (rj >= 0 && ((fmask >> rj) & 1u)) push(rj, qmask, seq);
                 }
                 if (qmask == 0 || counter >= kCounterLim) break;
-                int ei, ej, ekind;
+                int ei, ej, ekind, ecol;
                 T et;
-                pop(qmask, ei, ej, ekind, et);
+                pop(qmask, ei, ej, ekind, et, ecol);
                 ri = ei; rj = -1; owners = 0;  // nothing to re-scan unless the event executes
                 if ((ei == PK || ej == PK) && scored) {  // :230-231
                     ev_add(RGS_EV_DISCARDED);
@@ -1100,7 +1125,7 @@ struct LaneGame {
                 }
                 int goal = 0;
                 double dv_sq = -1.0;
-                rj = resolve(ei, ej, ekind, et, base, goal, dmg, live, &dv_sq);
+                rj = resolve(ei, ej, ekind, et, ecol, base, goal, dmg, live, &dv_sq);
                 if constexpr (kJamFF)
                     if (J.counter != 0) jam_log(J, ekind, ei, ej, goal, dv_sq);
                 if (goal) {
@@ -1128,6 +1153,7 @@ struct LaneGame {
     // returns the event-loop counter of the step (1 when nothing happened)
     RGS_DEV int step(double t_clock, double &sa, double &sb, double *dmg, long long live) const {
         if constexpr (kAbsClock) t0 = (T)t_clock;
+        tclk = t_clock;
         Bits<4 * E> wb;
         Bits<NPAIR> pb;
         step_head(wb, pb);
@@ -1250,6 +1276,10 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
     using S = LaneScratch<T, NT>;
     const LaneGame<T, NT, kNoise> G(P, tab, s);
     if constexpr (kNoise) G.nz_game = A.noise_game0 + game;
+#ifdef RGS_AB_EVLOCAL
+    int evloc[17];
+    G.evp = evloc;
+#endif
     double *srec = A.state + game * SREC;
 #pragma unroll 1
     for (int slot = 0; slot < E; ++slot) {
@@ -1269,11 +1299,11 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
     // with run-time indices), added to the game's int64 record at the end; the hash is carried over
     long long *gev = A.events + game * RGS_N_EVENTS;
 #pragma unroll 1
-    for (int i = 0; i < RGS_N_EVENTS; ++i) s.G(S::EVC + i) = 0;
+    for (int i = 0; i < RGS_N_EVENTS; ++i) G.EVW(i) = 0;
     {
         const unsigned long long h0 = (unsigned long long)gev[RGS_EV_HASH];
-        s.G(S::EVC + RGS_EV_HASH) = (int)(unsigned)h0;
-        s.G(S::EVC + 16) = (int)(unsigned)(h0 >> 32);
+        G.EVW(RGS_EV_HASH) = (int)(unsigned)h0;
+        G.EVW(16) = (int)(unsigned)(h0 >> 32);
     }
     double *dmg = A.damage + game * (NP * NP);
     long long live = gev[RGS_EV_LIVE_STEPS], loop_iters = gev[RGS_EV_LOOP_ITERS], decided = gev[RGS_EV_DECIDED_STEP];
@@ -1330,8 +1360,8 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
         else if (i == RGS_EV_LOOP_ITERS) v = loop_iters;
         else if (i == RGS_EV_DECIDED_STEP) v = decided;
         else if (i == RGS_EV_HASH)
-            v = (long long)(((unsigned long long)(unsigned)s.G(S::EVC + 16) << 32) | (unsigned)s.G(S::EVC + RGS_EV_HASH));
-        else v = gev[i] + (long long)s.G(S::EVC + i);
+            v = (long long)(((unsigned long long)(unsigned)G.EVW(16) << 32) | (unsigned)G.EVW(RGS_EV_HASH));
+        else v = gev[i] + (long long)G.EVW(i);
         gev[i] = v;
     }
 }

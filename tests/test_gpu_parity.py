@@ -326,7 +326,7 @@ def test_fast_nvn_tracks_oracle(rgs, n_team, n, steps):
     for name, r in (("fast64", g), ("fast", f)):
         er = r["events"].sum(0).astype(float)
         for k in ("WALL_UP", "WALL_DOWN", "WALL_RIGHT", "WALL_LEFT", "PLAYER_PLAYER", "PLAYER_PUCK"):
-            tol = 0.02 if name == "fast64" else 0.04
+            tol = 0.02 if name == "fast64" else 0.03
             assert abs(er[tl.EV[k]] - eo[tl.EV[k]]) <= tol * eo[tl.EV[k]] + 3 * np.sqrt(eo[tl.EV[k]] + 1), (name, k, eo[tl.EV[k]], er[tl.EV[k]])
         goals_o, goals_r = eo[0] + eo[1], er[0] + er[1]
         assert abs(goals_r - goals_o) < 5 * np.sqrt(goals_o + 1)
@@ -373,10 +373,10 @@ def test_fast32_score_distribution_vs_reference(rgs):
     assert abs(int(stats[2]) - int(fx["wins"][1])) <= 4 * np.sqrt(differ + 1)
     ev_g, ev_o = stats[8:22].astype(float), fx["events"][:14].astype(float)
     # Impact counts are dominated by RESTING contacts, whose event-loop length the reference decides by the rounding
-    # of its absolute fp64 clock (base_idx, src/GameSim.cpp:237; the reference with a step-relative clock counts 5 % fewer
-    # player-player impacts itself).  fp32 works in step-relative time, so those two counts are held to the measured
-    # gap (-3.9 % / -0.6 %), everything else to 1 %.
-    tol = {"PLAYER_PLAYER": 0.06, "PLAYER_PUCK": 0.02}
+    # of its absolute fp64 clock (base_idx, src/GameSim.cpp:237; run on a step-relative clock the reference itself
+    # counts 5 % fewer impacts).  fp32 event times are step-relative, but resolve() takes that one decision in fp64 on
+    # the reference's clock, so impacts track the reference too: 3 % here (chaotic games, different roundings).
+    tol = {"PLAYER_PLAYER": 0.03, "PLAYER_PUCK": 0.03}
     for k in ("WALL_UP", "WALL_DOWN", "WALL_RIGHT", "WALL_LEFT", "PLAYER_PLAYER", "PLAYER_PUCK", "GOALS_A", "GOALS_B"):
         assert abs(ev_g[tl.EV[k]] - ev_o[tl.EV[k]]) <= tol.get(k, 0.01) * ev_o[tl.EV[k]] + 3 * np.sqrt(ev_o[tl.EV[k]]), (k, ev_o[tl.EV[k]], ev_g[tl.EV[k]])
     # (b) independent sample, winning_score 4 (the 5x5 histogram) and 1 (wins A / B / undecided, time to the first goal:
@@ -649,7 +649,7 @@ def test_noise_through_the_drop_in_and_the_harness(rgs, tmp_path):
 
     a, b, c, quiet = play(1, 0.5), play(1, 0.5), play(2, 0.5), play(1, 0.0)
     assert np.array_equal(a, b) and not np.array_equal(a, c)
-    assert 1e-5 < np.abs(a - quiet).max() < 0.05 and np.allclose(a[:, 2:6], quiet[:, 2:6], atol=1e-9)   # puck: no noise
+    assert 1e-5 < np.abs(a - quiet).max() < 0.05 and np.allclose(a[:5, 2:6], quiet[:5, 2:6], atol=1e-9)   # puck: no noise of its own
     # sharding invariance: games 0..99 as one batch == two batches of 50 with game offsets 0 and 50
     n, steps, hold = 100, 60, 10
     xs, acts = tl.synth_inputs(5, 0, n, 2, steps // hold)
