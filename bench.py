@@ -213,6 +213,35 @@ def clocks_sampler_stop(p, f):
             "reasons": sorted(reasons)}
 
 
+def bind_to_gpu_numa_node(local_rank):
+    """Pin this rank (and therefore the first-touch placement of its pinned host buffers) to the CPUs of the NUMA node
+    its GPU hangs off: the end-to-end path stages ~1 GB per pass per GPU through host memory.  Returns what it did."""
+    try:
+        import torch
+
+        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id if hasattr(torch.cuda.get_device_properties(local_rank), "pci_bus_id") else None
+        if bus is None:
+            out = subprocess.run(["nvidia-smi", "-i", str(local_rank), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                                 stdout=subprocess.PIPE, text=True, timeout=20).stdout.strip()
+            bus = out[-12:] if out else None
+        if not bus:
+            return {"numa_node": None, "note": "no PCI bus id"}
+        path = f"/sys/bus/pci/devices/{bus.lower() if len(bus) == 12 else '0000:' + bus.lower()[-7:]}/numa_node"
+        node = int(open(path).read().strip())
+        if node < 0:
+            return {"numa_node": node, "note": "platform reports no NUMA affinity for the GPU"}
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+        return {"numa_node": node, "cpus": len(cpus)}
+    except Exception as exc:  # binding is an optimisation, never a failure
+        return {"numa_node": None, "note": f"{type(exc).__name__}: {exc}"[:120]}
+
+
 def main():
     args = parse()
     if args._worker:
@@ -244,6 +273,7 @@ def main():
         raise SystemExit("bench.py: no CUDA device; robo_game_sim_b200 has no CPU path")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else {"numa_node": None, "note": "single rank: not bound"}
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -319,15 +349,22 @@ def main():
         t0 = time.perf_counter()
         for _ in range(reps):
             _, _, hstats = sim.run_host(hx0, hact, H, hold=HOLD, out=out)
-        sec = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        my_sec = time.perf_counter() - t0
+        sec = torch.tensor([my_sec], dtype=torch.float64, device=dev)
         live = torch.tensor([int(hstats[_capi.ST_EVENTS0 + 10])], dtype=torch.int64, device=dev)
+        rank_secs = [sec.clone() for _ in range(world)]
         if world > 1:
+            dist.all_gather(rank_secs, sec)
             dist.all_reduce(sec, op=dist.ReduceOp.MAX)
             dist.all_reduce(live, op=dist.ReduceOp.SUM)
         esz = 4 if sim.action_dtype == torch.float32 else 8
         e2e = {"value": float(live.item()) * reps / float(sec.item()), "unit": "game-steps/s",
                "h2d_bytes_per_step": world * (G * 4 * 8 + G * n_act * 8 * esz),
                "d2h_bytes_per_step": world * (G * 22 * 8 + G * 16 * 8 + 96 * 8), "passes": reps,
+               # per-rank staging rates: (H2D + D2H bytes of one rank) / its own wall time per pass
+               "per_rank_host_gbs": [round((G * 4 * 8 + G * n_act * 8 * esz + G * 22 * 8 + G * 16 * 8) * reps / float(t.item()) / 1e9, 2)
+                                     for t in rank_secs],
+               "per_rank_pass_ms": [round(float(t.item()) / reps * 1e3, 2) for t in rank_secs], "numa": numa,
                "api": "BatchedGameSim.run_host -> rgs_batch_run_host (pinned host buffers, 8 game-range chunks "
                       "double-buffered over 2 streams)"}
 

@@ -207,9 +207,11 @@ int rgs_write_logs(const double *h_traj, int64_t n_games, int64_t n_rec, int32_t
  * h_x0_ball [n_games,4] doubles and h_actions [n_games,n_act,4n] (compute type) to the device in
  * chunks overlapped with compute, runs n_steps, and returns final states [n_games,2+4E] doubles,
  * events [n_games,RGS_N_EVENTS] and stats int64[RGS_N_STATS] into host buffers (any of the three
- * may be NULL).  Synchronous: returns when the outputs are valid. */
+ * may be NULL).  Synchronous: returns when the outputs are valid.  The copies and launches run on two private
+ * streams; they are ordered AFTER whatever the caller has queued on `stream` (the stream of its earlier asynchronous
+ * rgs_batch_run / _reset / _get calls on this batch; NULL = the legacy default stream). */
 int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_actions, int64_t n_act, int64_t hold,
-                       int64_t n_steps, double *h_state, int64_t *h_events, int64_t *h_stats);
+                       int64_t n_steps, double *h_state, int64_t *h_events, int64_t *h_stats, void *stream);
 
 /* Batch-of-one convenience used by the drop-in class robo_game_py.GameSim
  * (replaces reference src/RoboGamePy.cpp:15-24 one to one). */

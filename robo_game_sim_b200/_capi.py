@@ -60,7 +60,7 @@ SIGNATURES = {
     "rgs_synth_inputs": (C.c_int, [C.c_int, _u64, _i64, _i64, _i32, _i64, _dbl, _vp, _vp, _i32, _vp]),
     "rgs_measure_peak": (C.c_int, [C.c_int, _i32, C.POINTER(_dbl)]),
     "rgs_write_logs": (C.c_int, [_vp, _i64, _i64, _i32, _vp, C.c_char_p, _i64, _i32, _i32]),
-    "rgs_batch_run_host": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp]),
+    "rgs_batch_run_host": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
     "rgs_single_create": (C.c_int, [C.POINTER(_vp), C.c_int]),
     "rgs_single_destroy": (C.c_int, [_vp]),
     "rgs_single_reset": (C.c_int, [_vp, _dbl, _i32, C.POINTER(_dbl), _dbl, _i32, C.c_char_p, _i32, _dbl, _dbl, _dbl,

@@ -86,6 +86,7 @@ struct rgs_batch {
     double *stage_x0 = nullptr;
     cudaStream_t streams[2] = {nullptr, nullptr};
     cudaEvent_t done_ev[2] = {nullptr, nullptr};
+    cudaEvent_t order_ev = nullptr;
 };
 
 namespace {
@@ -126,8 +127,8 @@ int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64
     A.step0 = step0;
     A.u_max = u_max;
     if (synth == 2) {
-        if (b->p.mode == RGS_MODE_EXACT_F64 || b->n_team != 2)
-            return fail(RGS_EUNSUPPORTED, "the on-device policy runs in the FAST modes of the lane kernel with players_per_team == 2");
+        if (b->p.mode == RGS_MODE_EXACT_F64 || (b->n_team != 2 && b->p.noise != 0.0))
+            return fail(RGS_EUNSUPPORTED, "the on-device policy runs in the FAST modes (with process noise: players_per_team == 2 only)");
         A.pol = rgs::PolicyArgs{b->pol.kick_velocity, b->pol.gain, b->pol.input_limit, b->pol.safety_radius,
                                 b->pol.barrier_gain, b->pol.cbf, b->pol.sweeps, b->pol.kind};
     }
@@ -284,6 +285,7 @@ int rgs_batch_destroy(rgs_batch *b) {
         if (b->streams[k]) cudaStreamDestroy(b->streams[k]);
         if (b->done_ev[k]) cudaEventDestroy(b->done_ev[k]);
     }
+    if (b->order_ev) cudaEventDestroy(b->order_ev);
     delete b;
     return RGS_OK;
 }
@@ -446,7 +448,7 @@ int rgs_measure_peak(int device, int32_t fp64, double *out_tflops) {
 }
 
 int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_actions, int64_t n_act, int64_t hold,
-                       int64_t n_steps, double *h_state, int64_t *h_events, int64_t *h_stats) {
+                       int64_t n_steps, double *h_state, int64_t *h_events, int64_t *h_stats, void *stream) {
     int rc = check_run_args(b, n_act, hold, n_steps, 0, nullptr);
     if (rc != RGS_OK) return rc;
     if (!h_actions) return fail(RGS_EINVAL, "h_actions is NULL");
@@ -468,6 +470,12 @@ int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_acti
         if (!b->streams[k]) RGS_CUDA(cudaStreamCreateWithFlags(&b->streams[k], cudaStreamNonBlocking));
         if (!b->done_ev[k]) RGS_CUDA(cudaEventCreateWithFlags(&b->done_ev[k], cudaEventDisableTiming));
     }
+    // Work the caller queued on ITS stream for this batch (an asynchronous run / reset / get) must finish before the
+    // private streams touch the same records: they are non-blocking streams and do not synchronise with it implicitly.
+    if (!b->order_ev) RGS_CUDA(cudaEventCreateWithFlags(&b->order_ev, cudaEventDisableTiming));
+    RGS_CUDA(cudaEventRecord(b->order_ev, static_cast<cudaStream_t>(stream)));
+    RGS_CUDA(cudaStreamWaitEvent(b->streams[0], b->order_ev, 0));
+    RGS_CUDA(cudaStreamWaitEvent(b->streams[1], b->order_ev, 0));
     // Game-range chunks, double-buffered over two streams: the H2D copy of chunk c+1 and the D2H
     // copy of chunk c-1 overlap the rollout of chunk c (games are independent, so a chunk is
     // simply a contiguous slice of the batch).
@@ -595,6 +603,10 @@ int rgs_single_create(rgs_single **out, int device) {
     int rc = rgs_batch_create(&s->b_exact, device, 1, &s->p);
     if (rc != RGS_OK) { delete s; return rc; }
     s->b = s->b_exact;
+    {   // the create-time reset ran on the legacy stream; this handle works on its own non-blocking stream
+        DeviceGuard guard(device);
+        cudaDeviceSynchronize();
+    }
     DeviceGuard guard(device);
     cudaError_t e = cudaMalloc(&s->d_act, 8 * sizeof(double));
     if (e == cudaSuccess) e = cudaMalloc(&s->d_x0, 4 * sizeof(double));
@@ -637,6 +649,8 @@ int rgs_single_reset(rgs_single *s, double dt, int32_t winning_score, const doub
     if (noise != 0.0 && !s->b_noise) {
         int rcn = rgs_batch_create(&s->b_noise, s->device, 1, &p);
         if (rcn != RGS_OK) return rcn;
+        DeviceGuard guard(s->device);
+        cudaDeviceSynchronize();
     }
     s->b = noise != 0.0 ? s->b_noise : s->b_exact;
     p.tau_puck = tau_puck;

@@ -52,6 +52,13 @@
 #define RGS_DEV_BIG RGS_DEV
 #endif
 
+// A/B: cold paths (jam bookkeeping) compiled once and CALLED, to keep them out of the hot instruction stream
+#if defined(RGS_AB_COLDJAM) && !defined(RGS_HOST_EMU)
+#define RGS_DEV_COLD __device__ __noinline__
+#else
+#define RGS_DEV_COLD RGS_DEV
+#endif
+
 namespace rgs {
 
 constexpr int kJamLog = 6;   // longest period of a jammed event loop that is fast-forwarded (LaneGame::JamSnap)
@@ -250,9 +257,16 @@ struct LaneGame {
 
     // cumulative correctOverlap offset of body e at column c > CS[e]
     RGS_DEV void off_at(int e, int c, T &ox, T &oy) const {
+#ifdef RGS_AB_OFFSEL
+        const bool late = c >= s.I(S::FL + e);
+        ox = late ? s.F(S::OFF + 2 * e) : T(0);
+        oy = late ? s.F(S::OFF + 2 * e + 1) : T(0);
+        if (__builtin_expect(!late && c >= s.I(S::FF + e), 0)) { ox = s.TR(e, c, 0); oy = s.TR(e, c, 1); }
+#else
         if (c >= s.I(S::FL + e)) { ox = s.F(S::OFF + 2 * e); oy = s.F(S::OFF + 2 * e + 1); }
         else if (c < s.I(S::FF + e)) { ox = T(0); oy = T(0); }
         else { ox = s.TR(e, c, 0); oy = s.TR(e, c, 1); }
+#endif
     }
     RGS_DEV T off_at1(int e, int a, int c) const {
         if (c >= s.I(S::FL + e)) return s.F(S::OFF + 2 * e + a);
@@ -430,7 +444,13 @@ struct LaneGame {
     }
     // q and its velocity at column c >= cs (closed form from the segment start)
     RGS_DEV T axis_off(const Axis &A, int c) const {   // mirrored cumulative offset at column c
+#ifdef RGS_AB_OFFSEL
+        T o = c >= A.fl ? A.off_t : T(0);
+        if (__builtin_expect(c < A.fl && c >= A.ff, 0)) o = A.sgn * s.TR(A.e, c, A.ax);
+        return o;
+#else
         return c >= A.fl ? A.off_t : (c < A.ff ? T(0) : A.sgn * s.TR(A.e, c, A.ax));
+#endif
     }
     RGS_DEV void axis_at(const Axis &A, int c, T &q, T &v) const {
         const int j = c - A.cs;
@@ -546,11 +566,17 @@ struct LaneGame {
         }
         const LaneGK<T> gk = tab->e[g.ty][j];
         const T tj = P.d.dt_col * T(j);
+#ifdef RGS_AB_OFFSEL
+        const bool late = c >= g.fl;
+        T ox = late ? g.otx : T(0), oy = late ? g.oty : T(0);
+        if (__builtin_expect(!late && c >= g.ff, 0)) { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
+#else
         T ox = g.otx, oy = g.oty;
         if (c < g.fl) {
             if (c < g.ff) { ox = T(0); oy = T(0); }
             else { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
         }
+#endif
         px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + ox;
         py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + oy;
         if constexpr (kNoise)
@@ -567,11 +593,17 @@ struct LaneGame {
         }
         const LaneGK<T> gk = tab->e[g.ty][j];
         const T tj = P.d.dt_col * T(j);
+#ifdef RGS_AB_OFFSEL
+        const bool late = c >= g.fl;
+        T ox = late ? g.otx : T(0), oy = late ? g.oty : T(0);
+        if (__builtin_expect(!late && c >= g.ff, 0)) { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
+#else
         T ox = g.otx, oy = g.oty;
         if (c < g.fl) {
             if (c < g.ff) { ox = T(0); oy = T(0); }
             else { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
         }
+#endif
         px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + ox;
         py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + oy;
         vx = fm(g.wx, gk.g, g.ux);
@@ -994,7 +1026,7 @@ struct LaneGame {
         }
         return r;
     }
-    RGS_DEV void jam_snapshot(JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
+    RGS_DEV_COLD void jam_snapshot(JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
                               bool scored, int seq, int counter) const {
 #pragma unroll 1
         for (int w = 0; w < S::QT; ++w) JF(w) = s.F(w);
@@ -1013,7 +1045,7 @@ struct LaneGame {
         J.base = base; J.ri = ri; J.rj = rj; J.scored = scored; J.seq = seq; J.counter = counter;
         J.log_n = 0;
     }
-    RGS_DEV bool jam_same(const JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
+    RGS_DEV_COLD bool jam_same(const JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
                           bool scored) const {
         if (J.qmask != qmask || J.owners != owners || J.wbits != wbits || J.pbits != pbits || J.base != base || J.ri != ri ||
             J.rj != rj || J.scored != (int)scored)
@@ -1031,7 +1063,7 @@ struct LaneGame {
         return J.ranks == queue_ranks(qmask);
     }
     // skip the whole periods that fit before the loop bound; returns the new counter
-    RGS_DEV int jam_fast_forward(const JamSnap &J, int counter, int &seq, unsigned qmask, double *dmg, long long live) const {
+    RGS_DEV_COLD int jam_fast_forward(const JamSnap &J, int counter, int &seq, unsigned qmask, double *dmg, long long live) const {
         const int period = counter - J.counter;
         const int m = (kCounterLim - counter) / period;
         if (m <= 0 || J.log_n != period) return counter;

@@ -52,7 +52,13 @@ constexpr size_t lane_smem_bytes(int threads) {
 // 2v2 fp32) run 10 % faster than 64 (7 CTAs); 256 and 512 are level with 128, 192 / 320 / 384 clearly worse.
 // Records too large for two 128-lane CTAs per SM keep 64.
 template <typename T, int NT>
-constexpr int lane_big_threads() { return lane_smem_bytes<T, NT>(128) <= 110 * 1024 ? 128 : 64; }
+constexpr int lane_big_threads() {
+#ifdef RGS_AB_THREADS
+    return RGS_AB_THREADS;
+#else
+    return lane_smem_bytes<T, NT>(128) <= 110 * 1024 ? 128 : 64;
+#endif
+}
 
 constexpr int kSmallWarpsPerSm = 7;   // one-warp CTAs per SM aimed at by the small-batch path (see launch_lane_nt)
 
@@ -89,8 +95,8 @@ static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, c
 template <typename T, int NT, bool kNoise>
 static cudaError_t launch_lane_nt(const FastParams<T> &P, const RunArgs &A, cudaStream_t stream, int sm_count) {
     constexpr int kBig = lane_big_threads<T, NT>();
-    if (A.synth == 2) {  // closed loop on the on-device policy: instantiated for the reference's 2v2 only
-        if constexpr (NT == 2) return launch_lane_sized<T, NT, kBig, true, kNoise>(P, A, stream, sm_count);
+    if (A.synth == 2) {  // closed loop on the on-device policy (with process noise: the reference's 2v2 only)
+        if constexpr (NT == 2 || !kNoise) return launch_lane_sized<T, NT, kBig, true, kNoise>(P, A, stream, sm_count);
         else return cudaErrorNotSupported;
     }
     if (A.n_games < (int64_t)sm_count * kBig) {
@@ -113,7 +119,7 @@ static cudaError_t lane_scratch_nt(int sm_count, size_t *bytes) {
     cudaError_t err = lane_resident_ctas<T, NT, kBig, false, kNoise>(kBig, &per_sm);
     if (err != cudaSuccess) return err;
     int64_t threads = (int64_t)per_sm * kBig;
-    if constexpr (NT == 2) {
+    if constexpr (NT == 2 || !kNoise) {
         err = lane_resident_ctas<T, NT, kBig, true, kNoise>(kBig, &per_sm);
         if (err != cudaSuccess) return err;
         if ((int64_t)per_sm * kBig > threads) threads = (int64_t)per_sm * kBig;

@@ -233,7 +233,8 @@ class BatchedGameSim:
         """Closed loop on the on-device surrogate of the reference's baseline team (ClassicalTeam play logic and
         targets, closed-form tracking law; `cbf=1` adds the CBF.py barrier filter): the commands are computed from
         the state inside the kernel every step.  policy: kick_velocity, gain, input_limit, safety_radius,
-        barrier_gain, cbf, sweeps (include/rgs_capi.h rgs_policy).  FAST modes, 2 players per team."""
+        barrier_gain, cbf, sweeps, kind (include/rgs_capi.h rgs_policy).  FAST modes, any team size (player 1 of a team is
+        the goalie, the others field players); with process noise: 2 players per team."""
         torch = self._torch
         pol = _capi.RgsPolicy()
         self._lib.rgs_default_policy(C.byref(pol))
@@ -386,7 +387,7 @@ class BatchedGameSim:
             return x.data_ptr() if isinstance(x, torch.Tensor) else x.ctypes.data
 
         _capi.check(self._lib.rgs_batch_run_host(self._h, ptr(x0), ptr(a), a.shape[1], int(hold), int(n_steps), ptr(st),
-                                                 ptr(ev), stats.ctypes.data))
+                                                 ptr(ev), stats.ctypes.data, self._stream()))
         return st, ev, stats
 
 

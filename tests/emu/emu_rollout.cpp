@@ -34,8 +34,8 @@ void run_lane(const rgs_params &p, const rgs::RunArgs &A) {
     int iw[S::NI];
     std::vector<T> scr(S::SCR_WORDS_NOISE);   // the lane's global scratch area (tracks, event counters, jam snapshot, noise)
     S s{fw, iw, 1, scr.data(), 1};
-    if (A.synth == 2) {   // closed loop on the on-device surrogate policy (instantiated for 2v2, like the library)
-        if constexpr (NT == 2)
+    if (A.synth == 2) {   // closed loop on the on-device surrogate policy (with noise: 2v2 only, like the library)
+        if constexpr (NT == 2 || !kNoise)
             for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT, true, kNoise>(P, A, tab.get(), s, g);
     } else for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT, false, kNoise>(P, A, tab.get(), s, g);
 }
@@ -54,11 +54,19 @@ static rgs_policy g_policy;   // used by emu_rollout calls with synth == 2
 extern "C" void emu_set_policy(const rgs_policy *pol) { g_policy = *pol; }
 // the policy alone: commands [2 * 2n] of one game from its state record [2 + 4E] (fp64 arithmetic)
 extern "C" int emu_policy_commands(const rgs_params *p, const rgs_policy *pol, const double *state, double *u) {
-    if (p->players_per_team != 2) return -1;
     const rgs::DevParams<double> d = rgs::make_dev_params<double>(*p);
     const rgs::PolicyArgs a{pol->kick_velocity, pol->gain, pol->input_limit, pol->safety_radius, pol->barrier_gain, pol->cbf, pol->sweeps, pol->kind};
-    // state record: [TAS, TBS, puck, players...]; body index: players 0..3, puck 4
-    rgs::surrogate_policy<double, 2>(d, a, [&](int e, int c) { return state[2 + 4 * (e == 4 ? 0 : e + 1) + c]; }, u);
+    // state record: [TAS, TBS, puck, players...]; body index: players 0..2n-1, puck 2n
+    const int pk = 2 * p->players_per_team;
+    auto X = [&](int e, int c) { return state[2 + 4 * (e == pk ? 0 : e + 1) + c]; };
+    switch (p->players_per_team) {
+    case 1: rgs::surrogate_policy<double, 1>(d, a, X, u); break;
+    case 2: rgs::surrogate_policy<double, 2>(d, a, X, u); break;
+    case 3: rgs::surrogate_policy<double, 3>(d, a, X, u); break;
+    case 4: rgs::surrogate_policy<double, 4>(d, a, X, u); break;
+    case 7: rgs::surrogate_policy<double, 7>(d, a, X, u); break;
+    default: return -1;
+    }
     return 0;
 }
 
@@ -86,7 +94,7 @@ extern "C" int emu_rollout(const rgs_params *p, int64_t n_games, double *state, 
     A.step0 = step0;
     A.u_max = u_max;
     if (synth == 2) {
-        if (p->players_per_team != 2 || p->mode == RGS_MODE_EXACT_F64) return -2;
+        if (p->mode == RGS_MODE_EXACT_F64) return -2;
         A.pol = rgs::PolicyArgs{g_policy.kick_velocity, g_policy.gain, g_policy.input_limit, g_policy.safety_radius,
                                 g_policy.barrier_gain, g_policy.cbf, g_policy.sweeps, g_policy.kind};
     }

@@ -223,10 +223,11 @@ def emu_policy_commands(pd, pol, state):
     lib = emu_lib()
     p, q = rgs_params(pd), RgsPolicy(**pol)
     state = np.ascontiguousarray(state, dtype=np.float64)
-    u = np.zeros((state.shape[0], 8))
+    npl = 2 * pd["players_per_team"]
+    u = np.zeros((state.shape[0], 2 * npl))
     for g in range(state.shape[0]):
         assert lib.emu_policy_commands(C.byref(p), C.byref(q), _ptr(state[g]), _ptr(u[g])) == 0
-    return u.reshape(-1, 4, 2)
+    return u.reshape(-1, npl, 2)
 
 
 def emu_rollout(pd, state, actions, n_steps, hold=1, t=None, damage=None, events=None, log_stride=0, synth=None,

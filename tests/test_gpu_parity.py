@@ -776,7 +776,17 @@ def test_on_device_policy_closed_loop(rgs, tmp_path):
     with pytest.raises(RuntimeError, match="on-device policy"):
         rgs.BatchedGameSim(8, mode="exact").reset(x0_ball=np.zeros(4)).run_policy(5)
     with pytest.raises(RuntimeError, match="on-device policy"):
-        rgs.BatchedGameSim(8, mode="fast", players_per_team=3).reset(x0_ball=np.zeros(4)).run_policy(5)
+        rgs.BatchedGameSim(8, mode="fast", players_per_team=3, noise=0.5).reset(x0_ball=np.zeros(4)).run_policy(5)
+    # other team sizes (goalie + n-1 field players): GPU == emulator build, bit for bit, fp32 without the filter
+    for nt in (1, 3, 4):
+        xs, _ = tl.synth_inputs(33, 0, 256, nt, 1)
+        s3 = rgs.BatchedGameSim(256, mode="fast", players_per_team=nt, winning_score=3)
+        s3.reset(x0_ball=torch.from_numpy(xs).cuda())
+        s3.run_policy(100)
+        pdn = tl.default_params(n_team=nt, winning_score=3, mode=tl.MODE_FAST_F32)
+        en = tl.emu_rollout(pdn, tl.oracle_reset(pdn, xs), None, 100, policy=tl.default_policy())
+        assert np.array_equal(s3.state().cpu().numpy(), en["state"]) and np.array_equal(s3.events().cpu().numpy(), en["events"])
+        assert en["events"][:, tl.EV["PLAYER_PUCK"]].sum() > 0
     with pytest.raises(TypeError):
         sim.run_policy(5, kick=1.0)
     # the Monte Carlo harness, both teams on the device-side baseline policy (py/mc_example_1.py)

@@ -195,3 +195,43 @@ def test_dmpc_kind_follows_the_dmpc_play_logic_and_targets():
     r = tl.emu_rollout(dict(pd, mode=tl.MODE_FAST_F32, winning_score=3), tl.oracle_reset(tl.default_params(), x0), None, 200,
                        policy=tl.default_policy(kind=1, cbf=1))
     assert r["events"][:, tl.EV["PLAYER_PUCK"]].sum() > 100 and r["state"][:, :2].sum() >= 5
+
+
+@pytest.mark.parametrize("n_team", [1, 3, 4])
+def test_policy_for_other_team_sizes(n_team):
+    """The surrogate teams for n != 2 (roles of ClassicalTeam.py:44-75 generalised: player 1 of a team is the goalie,
+    the other n-1 are field players): the in-kernel closed loop equals stepping from the host with the policy's
+    commands (fp64, bit for bit, with and without the barrier filter), the field players follow the 2v2 field
+    player's law, and games are played out."""
+    pd = tl.default_params(n_team=n_team, mode=tl.MODE_FAST_F64, winning_score=2)
+    x0, _ = tl.synth_inputs(23, 0, 12, n_team, 1)
+    s0 = tl.oracle_reset(tl.default_params(n_team=n_team), x0)
+    for cbf in (0, 1):
+        pol = tl.default_policy(cbf=cbf)
+        a = tl.emu_rollout(pd, s0, None, 40, policy=pol)
+        st, t, dmg, ev = s0, None, None, None
+        for _ in range(40):
+            cmd = tl.emu_policy_commands(pd, pol, st)[:, None]
+            r = tl.emu_rollout(pd, st, cmd, 1, 1, t=t, damage=dmg, events=ev)
+            st, t, dmg, ev = r["state"], r["t"], r["damage"], r["events"]
+        assert np.array_equal(a["state"], st) and np.array_equal(a["events"], ev)
+    # every field player (q >= 1) of a team gets the command the 2v2 field player would get at its position
+    pol = tl.default_policy()
+    st = s0.copy()
+    st[:, 2:6] = np.random.default_rng(1).uniform([-4, -2, -2, -2], [4, 2, 2, 2], size=(12, 4))
+    u = tl.emu_policy_commands(pd, pol, st)
+    if n_team >= 3:
+        pd2 = tl.default_params(mode=tl.MODE_FAST_F64)
+        for team in (0, 1):
+            for q in range(1, n_team):
+                s2 = np.zeros((12, 22))
+                s2[:, :6] = st[:, :6]
+                for tt in (0, 1):       # goalie and the probed field player of each team
+                    s2[:, 6 + 8 * tt:10 + 8 * tt] = st[:, 6 + 4 * (tt * n_team):10 + 4 * (tt * n_team)]
+                    s2[:, 10 + 8 * tt:14 + 8 * tt] = st[:, 6 + 4 * (tt * n_team + q):10 + 4 * (tt * n_team + q)]
+                # the clearing direction looks at the adversary's first two players: same in both layouts
+                s2[:, 10 + 8 * (1 - team):14 + 8 * (1 - team)] = st[:, 6 + 4 * ((1 - team) * n_team + 1):10 + 4 * ((1 - team) * n_team + 1)]
+                u2 = tl.emu_policy_commands(pd2, pol, s2)
+                assert np.allclose(u[:, team * n_team + q], u2[:, team * 2 + 1], atol=1e-12)
+    played = tl.emu_rollout(dict(pd, mode=tl.MODE_FAST_F32, winning_score=3), s0, None, 200, policy=pol)
+    assert played["events"][:, tl.EV["PLAYER_PUCK"]].sum() > 0 and np.isfinite(played["state"]).all()
