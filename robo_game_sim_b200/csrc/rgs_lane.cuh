@@ -52,13 +52,6 @@
 #define RGS_DEV_BIG RGS_DEV
 #endif
 
-// A/B: cold paths (jam bookkeeping) compiled once and CALLED, to keep them out of the hot instruction stream
-#if defined(RGS_AB_COLDJAM) && !defined(RGS_HOST_EMU)
-#define RGS_DEV_COLD __device__ __noinline__
-#else
-#define RGS_DEV_COLD RGS_DEV
-#endif
-
 namespace rgs {
 
 constexpr int kJamLog = 6;   // longest period of a jammed event loop that is fast-forwarded (LaneGame::JamSnap)
@@ -257,16 +250,10 @@ struct LaneGame {
 
     // cumulative correctOverlap offset of body e at column c > CS[e]
     RGS_DEV void off_at(int e, int c, T &ox, T &oy) const {
-#ifdef RGS_AB_OFFSEL
         const bool late = c >= s.I(S::FL + e);
         ox = late ? s.F(S::OFF + 2 * e) : T(0);
         oy = late ? s.F(S::OFF + 2 * e + 1) : T(0);
         if (__builtin_expect(!late && c >= s.I(S::FF + e), 0)) { ox = s.TR(e, c, 0); oy = s.TR(e, c, 1); }
-#else
-        if (c >= s.I(S::FL + e)) { ox = s.F(S::OFF + 2 * e); oy = s.F(S::OFF + 2 * e + 1); }
-        else if (c < s.I(S::FF + e)) { ox = T(0); oy = T(0); }
-        else { ox = s.TR(e, c, 0); oy = s.TR(e, c, 1); }
-#endif
     }
     RGS_DEV T off_at1(int e, int a, int c) const {
         if (c >= s.I(S::FL + e)) return s.F(S::OFF + 2 * e + a);
@@ -298,12 +285,7 @@ struct LaneGame {
 
     // event record of the launch: 32-bit counters (RGS_EV_* order; [RGS_EV_HASH], [16] = hash lo, hi), added to the game's
     // int64 record at the end
-#ifdef RGS_AB_EVLOCAL
-    mutable int *evp = nullptr;
-    RGS_DEV int &EVW(int k) const { return evp[k]; }
-#else
     RGS_DEV int &EVW(int k) const { return s.G(S::EVC + k); }
-#endif
     RGS_DEV void ev_add(int k, int n = 1) const { EVW(k) += n; }
     RGS_DEV void hash_ev(long long live, int kind, int i, int j, int goal) const {
         unsigned long long h = ((unsigned long long)(unsigned)EVW(16) << 32) | (unsigned)EVW(RGS_EV_HASH);
@@ -444,13 +426,9 @@ struct LaneGame {
     }
     // q and its velocity at column c >= cs (closed form from the segment start)
     RGS_DEV T axis_off(const Axis &A, int c) const {   // mirrored cumulative offset at column c
-#ifdef RGS_AB_OFFSEL
         T o = c >= A.fl ? A.off_t : T(0);
         if (__builtin_expect(c < A.fl && c >= A.ff, 0)) o = A.sgn * s.TR(A.e, c, A.ax);
         return o;
-#else
-        return c >= A.fl ? A.off_t : (c < A.ff ? T(0) : A.sgn * s.TR(A.e, c, A.ax));
-#endif
     }
     RGS_DEV void axis_at(const Axis &A, int c, T &q, T &v) const {
         const int j = c - A.cs;
@@ -566,17 +544,9 @@ struct LaneGame {
         }
         const LaneGK<T> gk = tab->e[g.ty][j];
         const T tj = P.d.dt_col * T(j);
-#ifdef RGS_AB_OFFSEL
         const bool late = c >= g.fl;
         T ox = late ? g.otx : T(0), oy = late ? g.oty : T(0);
         if (__builtin_expect(!late && c >= g.ff, 0)) { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
-#else
-        T ox = g.otx, oy = g.oty;
-        if (c < g.fl) {
-            if (c < g.ff) { ox = T(0); oy = T(0); }
-            else { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
-        }
-#endif
         px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + ox;
         py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + oy;
         if constexpr (kNoise)
@@ -593,17 +563,9 @@ struct LaneGame {
         }
         const LaneGK<T> gk = tab->e[g.ty][j];
         const T tj = P.d.dt_col * T(j);
-#ifdef RGS_AB_OFFSEL
         const bool late = c >= g.fl;
         T ox = late ? g.otx : T(0), oy = late ? g.oty : T(0);
         if (__builtin_expect(!late && c >= g.ff, 0)) { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
-#else
-        T ox = g.otx, oy = g.oty;
-        if (c < g.fl) {
-            if (c < g.ff) { ox = T(0); oy = T(0); }
-            else { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
-        }
-#endif
         px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + ox;
         py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + oy;
         vx = fm(g.wx, gk.g, g.ux);
@@ -861,11 +823,19 @@ struct LaneGame {
             // decides between column i-1 and i, which sets how long a jammed event loop runs.  fp32 event times are
             // step-relative; that one decision (and dt_t, :254) is taken in fp64 exactly as the reference takes it.
             const T tau = et - col_time(ecol - 1);
-            const double tcol = (tclk + P.dt_col64 * (double)(ecol - 1)) + (double)tau;
-            int nb = (int)floor((tcol - tclk) / P.dt_col64) + 1;
-            if (nb > kGrid) { nb = kGrid; ev_add(RGS_EV_BASE_CLAMP); }
-            if (nb > base) base = nb;
-            dt_t = (T)(tcol - (tclk + P.dt_col64 * (double)(base - 1)));
+            int nb;
+            if (tau == T(0)) {   // resting contact: the reference's clock rounding decides
+                const double tcol = tclk + P.dt_col64 * (double)(ecol - 1);
+                nb = (int)floor((tcol - tclk) / P.dt_col64) + 1;
+                if (nb > kGrid) { nb = kGrid; ev_add(RGS_EV_BASE_CLAMP); }
+                if (nb > base) base = nb;
+                dt_t = (T)(tcol - (tclk + P.dt_col64 * (double)(base - 1)));
+            } else {
+                nb = (int)floor(et / P.d.dt_col) + 1;
+                if (nb > kGrid) { nb = kGrid; ev_add(RGS_EV_BASE_CLAMP); }
+                if (nb > base) base = nb;
+                dt_t = et - col_time(base - 1);
+            }
         }
         const T h_rest = P.d.dt_col - dt_t;
         const int tyi = (ei == PK);
@@ -1026,7 +996,7 @@ struct LaneGame {
         }
         return r;
     }
-    RGS_DEV_COLD void jam_snapshot(JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
+    RGS_DEV void jam_snapshot(JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
                               bool scored, int seq, int counter) const {
 #pragma unroll 1
         for (int w = 0; w < S::QT; ++w) JF(w) = s.F(w);
@@ -1045,7 +1015,7 @@ struct LaneGame {
         J.base = base; J.ri = ri; J.rj = rj; J.scored = scored; J.seq = seq; J.counter = counter;
         J.log_n = 0;
     }
-    RGS_DEV_COLD bool jam_same(const JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
+    RGS_DEV bool jam_same(const JamSnap &J, unsigned qmask, unsigned owners, unsigned wbits, unsigned pbits, int base, int ri, int rj,
                           bool scored) const {
         if (J.qmask != qmask || J.owners != owners || J.wbits != wbits || J.pbits != pbits || J.base != base || J.ri != ri ||
             J.rj != rj || J.scored != (int)scored)
@@ -1063,7 +1033,7 @@ struct LaneGame {
         return J.ranks == queue_ranks(qmask);
     }
     // skip the whole periods that fit before the loop bound; returns the new counter
-    RGS_DEV_COLD int jam_fast_forward(const JamSnap &J, int counter, int &seq, unsigned qmask, double *dmg, long long live) const {
+    RGS_DEV int jam_fast_forward(const JamSnap &J, int counter, int &seq, unsigned qmask, double *dmg, long long live) const {
         const int period = counter - J.counter;
         const int m = (kCounterLim - counter) / period;
         if (m <= 0 || J.log_n != period) return counter;
@@ -1308,10 +1278,6 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
     using S = LaneScratch<T, NT>;
     const LaneGame<T, NT, kNoise> G(P, tab, s);
     if constexpr (kNoise) G.nz_game = A.noise_game0 + game;
-#ifdef RGS_AB_EVLOCAL
-    int evloc[17];
-    G.evp = evloc;
-#endif
     double *srec = A.state + game * SREC;
 #pragma unroll 1
     for (int slot = 0; slot < E; ++slot) {
