@@ -38,7 +38,7 @@ struct FastParams {
     T nz_end[3];                 // same for the noise accumulated over a whole game-step (50 sub-steps)
     T nz_env;                    // 6.5 standard deviations of the accumulated position noise (broad-phase envelope)
     uint32_t seed_lo, seed_hi;   // reset()'s seed
-    double dt_col64;             // dt / 50 in fp64 (the reference's dt_col_, :28), for the base_idx decision of resolve()
+    double dt_col64, inv_dt_col64;  // dt / 50 in fp64 (the reference's dt_col_, :28) and RN(1 / dt_col_): base_idx decision of resolve()
 };
 
 // The reference adds sigma * N(0,1) to both player accelerations on EVERY f_player call, i.e. on each of the four

@@ -114,6 +114,7 @@ inline FastParams<T> make_fast_params(const rgs_params &p) {
         f.nz_end[0] = T(sg * e11); f.nz_end[1] = T(sg * e21); f.nz_end[2] = T(sg * e22);
         f.nz_env = T(6.5 * std::fabs(sg) * std::sqrt(Spp));
         f.dt_col64 = p.dt / RGS_GRID_POINTS;
+        f.inv_dt_col64 = 1.0 / f.dt_col64;
         f.seed_lo = (uint32_t)p.seed;
         f.seed_hi = 0x5EEDu;
     }

@@ -826,7 +826,11 @@ struct LaneGame {
             int nb;
             if (tau == T(0)) {   // resting contact: the reference's clock rounding decides
                 const double tcol = tclk + P.dt_col64 * (double)(ecol - 1);
-                nb = (int)floor((tcol - tclk) / P.dt_col64) + 1;
+                // (t_col - t_) / dt_col_, correctly rounded without nvcc's division expansion (whose slow path a zero
+                // numerator -- a contact resting at column 1 -- would take): quotient correction with y = RN(1 / dt_col_)
+                const double x = tcol - tclk, q0 = x * P.inv_dt_col64;
+                const double q = x == 0.0 ? 0.0 : fm(fm(-P.dt_col64, q0, x), P.inv_dt_col64, q0);
+                nb = (int)floor(q) + 1;
                 if (nb > kGrid) { nb = kGrid; ev_add(RGS_EV_BASE_CLAMP); }
                 if (nb > base) base = nb;
                 dt_t = (T)(tcol - (tclk + P.dt_col64 * (double)(base - 1)));
