@@ -120,6 +120,7 @@ int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64
     A.act_game_stride = act_game_stride;
     A.n_steps = n_steps;
     A.log_stride = log_stride;
+    A.traj_recs = log_stride > 0 ? n_steps / log_stride : 0;
     A.traj = d_traj ? d_traj + g0 * (n_steps / (log_stride > 0 ? log_stride : 1)) * (1 + b->srec + np * np) : nullptr;
     A.synth = synth;
     A.seed = seed;

@@ -72,6 +72,7 @@ struct RunArgs {
     int64_t n_act, hold, act_game_stride;
     int64_t n_steps, log_stride;
     double *traj;
+    int64_t traj_recs;  // trajectory records per game = n_steps / log_stride (0 when not logging)
     // command source: 0 the action tensor, 1 on-chip synthetic actions, 2 the on-device policy `pol` (K2 lane kernel)
     int synth;
     uint64_t seed;
@@ -87,6 +88,7 @@ struct RunArgs {
 // ---- Philox4x32-10 (Salmon et al. 2011), counter-based: keyed by (seed, game, action index) ----
 __host__ __device__ inline void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
                                               uint32_t k1, uint32_t out[4]) {
+#pragma unroll 1   // rolled: the generator sits in the rollout kernels' step loop but runs once per `hold` steps
     for (int r = 0; r < 10; ++r) {
         const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
         const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;

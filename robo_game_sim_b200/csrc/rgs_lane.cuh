@@ -824,7 +824,11 @@ struct LaneGame {
             // step-relative; that one decision (and dt_t, :254) is taken in fp64 exactly as the reference takes it.
             const T tau = et - col_time(ecol - 1);
             int nb;
+#ifdef RGS_AB_NO64BASE
+            if (false) {
+#else
             if (tau == T(0)) {   // resting contact: the reference's clock rounding decides
+#endif
                 const double tcol = tclk + P.dt_col64 * (double)(ecol - 1);
                 // (t_col - t_) / dt_col_, correctly rounded without nvcc's division expansion (whose slow path a zero
                 // numerator -- a contact resting at column 1 -- would take): quotient correction with y = RN(1 / dt_col_)
@@ -1250,19 +1254,26 @@ struct LaneGame {
 };
 
 // trajectory record [t, state (reference order), damage] after step k
+// (compiled once and CALLED: the rollout kernels are instruction-fetch-bound with a cliff at 64 KB of code,
+// profiles/r02_ab_variants.md, and a non-logging launch never comes here)
+#ifdef RGS_HOST_EMU
+#define RGS_DEV_CALLED inline
+#else
+#define RGS_DEV_CALLED __device__ __noinline__
+#endif
 template <typename T, int NT>
-RGS_DEV void write_traj_lane(const RunArgs &A, const LaneScratch<T, NT> &s, int64_t game, int64_t k, double t_clock, double sa,
-                             double sb) {
+RGS_DEV_CALLED void write_traj_lane(const RunArgs &A, const LaneScratch<T, NT> s, int64_t game, int64_t rec_idx, double t_clock,
+                                    double sa, double sb) {
     constexpr int E = 2 * NT + 1, PK = 2 * NT, SREC = 2 + 4 * E, NP = 2 * NT, TREC = 1 + SREC + NP * NP;
     using S = LaneScratch<T, NT>;
-    double *rec = A.traj + (game * (A.n_steps / A.log_stride) + ((k + 1) / A.log_stride - 1)) * TREC;
+    double *rec = A.traj + (game * A.traj_recs + rec_idx) * TREC;   // record rec_idx of this game (no 64-bit divisions here)
     rec[0] = t_clock;
     rec[1] = sa;
     rec[2] = sb;
 #pragma unroll 1
     for (int slot = 0; slot < E; ++slot) {
         const int e = slot == 0 ? PK : slot - 1;
-#pragma unroll
+#pragma unroll 1
         for (int c = 0; c < 4; ++c) rec[3 + 4 * slot + c] = (double)s.F(S::SP + 4 * e + c);
     }
 #pragma unroll 1
@@ -1316,7 +1327,7 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
     int64_t phase = A.synth ? A.step0 % A.hold : 0;
     bool fetch = true;
     const bool logging = A.traj != nullptr && A.log_stride > 0;
-    int64_t k = 0, log_left = A.log_stride;
+    int64_t k = 0, log_left = A.log_stride, log_rec = 0;
 #pragma unroll 1
     for (; k < A.n_steps; ++k) {
         if (!(sa < wsc && sb < wsc)) break;  // undecided(), :57-60
@@ -1340,12 +1351,12 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
         if (decided == 0 && !(sa < wsc && sb < wsc)) decided = live;
         if (logging && --log_left == 0) {
             log_left = A.log_stride;
-            write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb);
+            write_traj_lane<T, NT>(A, s, game, log_rec++, t_clock, sa, sb);
         }
     }
     if (logging)  // frozen steps of a decided game (GameSim::run :121-123) repeat the frozen state
         for (; k < A.n_steps; ++k)
-            if (--log_left == 0) { log_left = A.log_stride; write_traj_lane<T, NT>(A, s, game, k, t_clock, sa, sb); }
+            if (--log_left == 0) { log_left = A.log_stride; write_traj_lane<T, NT>(A, s, game, log_rec++, t_clock, sa, sb); }
     srec[0] = sa;
     srec[1] = sb;
 #pragma unroll 1

@@ -28,9 +28,11 @@ __global__ void __launch_bounds__(THREADS, sizeof(T) == 4 ? 512 / THREADS : 1) r
     extern __shared__ __align__(16) unsigned char smem_raw[];
     LaneTab<T> *tab = reinterpret_cast<LaneTab<T> *>(smem_raw);
     constexpr size_t tab_bytes = (sizeof(LaneTab<T>) + 15) & ~size_t(15);
+    // the record layout always has THREADS slots (a compile-time word stride keeps the address arithmetic out of the
+    // code); in the one-warp instantiation only the first `lanes` of them carry a game
     const int per_cta = THREADS == 32 ? lanes : THREADS;
     T *fw = reinterpret_cast<T *>(smem_raw + tab_bytes);
-    int *iw = reinterpret_cast<int *>(fw + (size_t)S::NF * per_cta);
+    int *iw = reinterpret_cast<int *>(fw + (size_t)S::NF * THREADS);
     for (int i = threadIdx.x; i < 2 * kCols; i += THREADS) {
         (&tab->e[0][0])[i].g = (&P.tab_g[0][0])[i];
         (&tab->e[0][0])[i].k = (&P.tab_k[0][0])[i];
@@ -40,7 +42,7 @@ __global__ void __launch_bounds__(THREADS, sizeof(T) == 4 ? 512 / THREADS : 1) r
     const size_t warp = ((size_t)blockIdx.x * THREADS + threadIdx.x) >> 5;
     constexpr size_t scr_words = kNoise ? S::SCR_WORDS_NOISE : S::SCR_WORDS;
     T *scr = static_cast<T *>(A.lane_scratch) + warp * (scr_words * 32) + (threadIdx.x & 31);
-    const S s{fw + threadIdx.x, iw + threadIdx.x, per_cta, scr, 32};
+    const S s{fw + threadIdx.x, iw + threadIdx.x, THREADS, scr, 32};
     const int64_t stride = (int64_t)gridDim.x * per_cta;
     for (int64_t game = (int64_t)blockIdx.x * per_cta + threadIdx.x; game < A.n_games; game += stride)
         rollout_lane_game<T, NT, kPolicy, kNoise>(P, A, tab, s, game);
@@ -68,7 +70,8 @@ constexpr int kSmallWarpsPerSm = 7;   // one-warp CTAs per SM aimed at by the sm
 
 template <typename T, int NT, int kThreads, bool kPolicy, bool kNoise>
 static cudaError_t lane_resident_ctas(int lanes, int *per_sm) {
-    const size_t smem = lane_smem_bytes<T, NT>(lanes);
+    (void)lanes;
+    const size_t smem = lane_smem_bytes<T, NT>(kThreads);
     auto kern = rollout_lane_kernel<T, NT, kThreads, kPolicy, kNoise>;
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
@@ -90,7 +93,7 @@ static cudaError_t launch_lane_sized(const FastParams<T> &P, const RunArgs &A, c
     const size_t words = kNoise ? LaneScratch<T, NT>::SCR_WORDS_NOISE : LaneScratch<T, NT>::SCR_WORDS;
     const size_t need = (size_t)blocks * kThreads * words * sizeof(T);
     if (!A.lane_scratch || A.lane_scratch_bytes < need) return cudaErrorInvalidValue;
-    rollout_lane_kernel<T, NT, kThreads, kPolicy, kNoise><<<(unsigned)blocks, kThreads, lane_smem_bytes<T, NT>(lanes), stream>>>(P, A, lanes);
+    rollout_lane_kernel<T, NT, kThreads, kPolicy, kNoise><<<(unsigned)blocks, kThreads, lane_smem_bytes<T, NT>(kThreads), stream>>>(P, A, lanes);
     return cudaGetLastError();
 }
 
@@ -138,6 +141,10 @@ static cudaError_t lane_scratch_nt(int sm_count, size_t *bytes) {
 template <typename T, typename F>
 static cudaError_t by_team(int n_team, F &&f) {
     switch (n_team) {
+#ifdef RGS_AB_ONLY_2V2   // size / A-B builds only (tools/sass_size.sh): compile the reference's team size alone
+    case 2: return f(std::integral_constant<int, 2>{});
+    default: return cudaErrorInvalidValue;
+#else
     case 1: return f(std::integral_constant<int, 1>{});
     case 2: return f(std::integral_constant<int, 2>{});
     case 3: return f(std::integral_constant<int, 3>{});
@@ -146,6 +153,7 @@ static cudaError_t by_team(int n_team, F &&f) {
     case 6: return f(std::integral_constant<int, 6>{});
     case 7: return f(std::integral_constant<int, 7>{});
     default: return cudaErrorInvalidValue;
+#endif
     }
 }
 

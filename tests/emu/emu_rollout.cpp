@@ -86,6 +86,7 @@ extern "C" int emu_rollout(const rgs_params *p, int64_t n_games, double *state, 
     A.act_game_stride = act_game_stride;
     A.n_steps = n_steps;
     A.log_stride = log_stride;
+    A.traj_recs = log_stride > 0 ? n_steps / log_stride : 0;
     A.traj = traj;
     A.synth = synth;
     A.seed = seed;
