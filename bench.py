@@ -219,14 +219,10 @@ def bind_to_gpu_numa_node(local_rank):
     try:
         import torch
 
-        bus = torch.cuda.get_device_properties(local_rank).pci_bus_id if hasattr(torch.cuda.get_device_properties(local_rank), "pci_bus_id") else None
-        if bus is None:
-            out = subprocess.run(["nvidia-smi", "-i", str(local_rank), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
-                                 stdout=subprocess.PIPE, text=True, timeout=20).stdout.strip()
-            bus = out[-12:] if out else None
-        if not bus:
-            return {"numa_node": None, "note": "no PCI bus id"}
-        path = f"/sys/bus/pci/devices/{bus.lower() if len(bus) == 12 else '0000:' + bus.lower()[-7:]}/numa_node"
+        pr = torch.cuda.get_device_properties(local_rank)
+        if not all(hasattr(pr, k) for k in ("pci_domain_id", "pci_bus_id", "pci_device_id")):
+            return {"numa_node": None, "note": "no PCI ids in the device properties"}
+        path = f"/sys/bus/pci/devices/{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0/numa_node"
         node = int(open(path).read().strip())
         if node < 0:
             return {"numa_node": node, "note": "platform reports no NUMA affinity for the GPU"}

@@ -36,7 +36,7 @@
 // column, :292-297, :336-340), so a body pressed against a wall or another body is corrected on every column.  The
 // segment keeps the total offset (in force from the column of the last fix on), the column of the first fix (no
 // offset before it) and, only when a segment has been fixed more than once, the cumulative offset of the columns in
-// between in a per-lane TRACK in global memory (LaneScratch::trk; lane-interleaved, touched by such bodies only).
+// between in a per-lane TRACK in global memory (LaneScratch::trk; contiguous per lane, touched by such bodies only).
 //
 // Everything is plain scalar C++ over a per-game scratch record, so tests/emu compiles the same
 // source with g++ (no warp emulation needed).  All fused multiply-adds are spelled out (fm()).
@@ -74,7 +74,9 @@ struct LaneScratch {
     static constexpr int QI = 2 * E;     // [e] (seq << 12) | (col << 6)... see q_pack
     static constexpr int FF = 3 * E;     // [e] column of the first correctOverlap fix (= CS when none)
     static constexpr int NI = 4 * E;
-    // per-lane global scratch area, in T-sized words ([word][lane] inside a warp): the tracks; the event counters of
+    // per-lane global scratch area, in T-sized words, contiguous per lane (the event path touches it from divergent
+    // code, one lane at a time and mostly column after column, so lane-major keeps its sectors dense): the tracks; the
+    // event counters of
     // this launch (RGS_EV_* order; [RGS_EV_HASH], [16] = hash lo, hi) and the per-body checksum of the track words
     // written for the segment (jam detection) as ints; then the jam snapshot (LaneGame::JamSnap).  All of it is touched
     // by the event path only -- the shared-memory record above is sized for 4 resident 128-lane CTAs per SM.
@@ -89,12 +91,11 @@ struct LaneScratch {
     T *f;
     int *i;
     int stride;
-    T *trk;        // cumulative offset of column c, axis a of body e at trk[((e * kCols + c) * 2 + a) * tstride]
-    int tstride;
-    RGS_DEV T &TR(int e, int c, int a) const { return trk[(size_t)((e * kCols + c) * 2 + a) * tstride]; }
+    T *trk;        // this lane's global scratch area; cumulative offset of column c, axis a of body e at trk[(e * kCols + c) * 2 + a]
+    RGS_DEV T &TR(int e, int c, int a) const { return trk[(e * kCols + c) * 2 + a]; }
     RGS_DEV T &F(int w) const { return f[w * stride]; }
     RGS_DEV int &I(int w) const { return i[w * stride]; }
-    RGS_DEV int &G(int w) const { return *reinterpret_cast<int *>(&trk[(size_t)w * tstride]); }   // int word of the global area
+    RGS_DEV int &G(int w) const { return *reinterpret_cast<int *>(&trk[w]); }   // int word of the global area
 };
 
 // index of the lowest set bit of a non-zero mask
@@ -220,7 +221,7 @@ struct LaneGame {
     mutable long long nz_game = 0;        // global game index
     mutable unsigned nz_step = 0, nz_epoch = 0;
     mutable bool nz_on = false;           // false while a quiet step commits from the closed form
-    RGS_DEV T &NZ(int e, int c, int k) const { return s.trk[(size_t)(S::NZ0 + (e * kCols + c) * 4 + k) * s.tstride]; }
+    RGS_DEV T &NZ(int e, int c, int k) const { return s.trk[S::NZ0 + (e * kCols + c) * 4 + k]; }
     RGS_DEV void gen_noise_path(int e, int c0) const {
         T npx = T(0), npy = T(0), nvx = T(0), nvy = T(0);
         NZ(e, c0, 0) = T(0); NZ(e, c0, 1) = T(0); NZ(e, c0, 2) = T(0); NZ(e, c0, 3) = T(0);
@@ -977,7 +978,7 @@ struct LaneGame {
     // counters [17]; per logged event kind | i << 4 | (j + 1) << 8 | goal << 12 [kJamLog] and the two halves of
     // dv_sq of a player-player impact (-1: none) [2 kJamLog]
     static constexpr int JI_EV = 5 * E, JI_LOG = 5 * E + 17, JI_DV = JI_LOG + kJamLog;
-    RGS_DEV T &JF(int w) const { return s.trk[(size_t)(S::JAM0 + w) * s.tstride]; }
+    RGS_DEV T &JF(int w) const { return s.trk[S::JAM0 + w]; }
     RGS_DEV int &JI(int w) const { return s.G(S::JAM0 + S::JAM_F + w); }
     static RGS_DEV bool same_bits(T a, T b) {
         if constexpr (sizeof(T) == 4) {

@@ -6,7 +6,7 @@
 // out word-major ([word][thread]) so that the run-time body indices of the event path never cause
 // a bank conflict (bank = lane) and never force per-thread arrays into local memory.
 // Global memory per resident lane: LaneScratch::SCR_WORDS words (correctOverlap tracks + jam snapshot),
-// lane-interleaved inside a warp ([word][lane]); touched only by bodies that are corrected repeatedly.
+// contiguous per lane; touched by the event path only.
 #pragma once
 #include <type_traits>
 
@@ -39,10 +39,9 @@ __global__ void __launch_bounds__(THREADS, sizeof(T) == 4 ? 512 / THREADS : 1) r
     }
     __syncthreads();
     if ((int)threadIdx.x >= per_cta) return;
-    const size_t warp = ((size_t)blockIdx.x * THREADS + threadIdx.x) >> 5;
     constexpr size_t scr_words = kNoise ? S::SCR_WORDS_NOISE : S::SCR_WORDS;
-    T *scr = static_cast<T *>(A.lane_scratch) + warp * (scr_words * 32) + (threadIdx.x & 31);
-    const S s{fw + threadIdx.x, iw + threadIdx.x, THREADS, scr, 32};
+    T *scr = static_cast<T *>(A.lane_scratch) + ((size_t)blockIdx.x * THREADS + threadIdx.x) * scr_words;
+    const S s{fw + threadIdx.x, iw + threadIdx.x, THREADS, scr};
     const int64_t stride = (int64_t)gridDim.x * per_cta;
     for (int64_t game = (int64_t)blockIdx.x * per_cta + threadIdx.x; game < A.n_games; game += stride)
         rollout_lane_game<T, NT, kPolicy, kNoise>(P, A, tab, s, game);

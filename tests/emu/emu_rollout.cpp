@@ -33,7 +33,7 @@ void run_lane(const rgs_params &p, const rgs::RunArgs &A) {
     T fw[S::NF];
     int iw[S::NI];
     std::vector<T> scr(S::SCR_WORDS_NOISE);   // the lane's global scratch area (tracks, event counters, jam snapshot, noise)
-    S s{fw, iw, 1, scr.data(), 1};
+    S s{fw, iw, 1, scr.data()};
     if (A.synth == 2) {   // closed loop on the on-device surrogate policy (with noise: 2v2 only, like the library)
         if constexpr (NT == 2 || !kNoise)
             for (int64_t g = 0; g < A.n_games; ++g) rgs::rollout_lane_game<T, NT, true, kNoise>(P, A, tab.get(), s, g);
