@@ -5,8 +5,14 @@
 
 namespace rgs {
 
+// resident CTAs per SM: the RK4 chains are latency-bound (largest stall: `wait` on dependent fp64 operations), so for
+// the small grids (1v1, 2v2: 35 KB of shared memory per CTA) five CTAs at <= 96 registers beat four at 112
+// (+7 %, profiles/r02_ab_variants.md); six (<= 80 registers, spills) do not.  Larger teams are shared-memory-limited.
+#ifndef RGS_AB_K1_MINBLOCKS
+#define RGS_AB_K1_MINBLOCKS (NT <= 2 ? 5 : 1)
+#endif
 template <int NT>
-__global__ void __launch_bounds__(128) rollout_exact_kernel(const __grid_constant__ DevParams<double> P,
+__global__ void __launch_bounds__(128, RGS_AB_K1_MINBLOCKS) rollout_exact_kernel(const __grid_constant__ DevParams<double> P,
                                                             const __grid_constant__ RunArgs A) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;

@@ -288,21 +288,24 @@ struct LaneGame {
     // int64 record at the end
     RGS_DEV int &EVW(int k) const { return s.G(S::EVC + k); }
     RGS_DEV void ev_add(int k, int n = 1) const { EVW(k) += n; }
+    mutable unsigned long long ev_hash = 0;   // the order-sensitive event hash of the game (RGS_EV_HASH), carried in registers
     RGS_DEV void hash_ev(long long live, int kind, int i, int j, int goal) const {
-        unsigned long long h = ((unsigned long long)(unsigned)EVW(16) << 32) | (unsigned)EVW(RGS_EV_HASH);
+        unsigned long long h = ev_hash;
         h ^= ((unsigned long long)live << 16) | ((unsigned long long)kind << 12) | ((unsigned long long)i << 8) |
              ((unsigned long long)(j < 0 ? 15 : j) << 4) | (unsigned long long)goal;   // == hash_event() of rgs_device.cuh
         h *= 0x100000001B3ULL;
-        EVW(RGS_EV_HASH) = (int)(unsigned)h;
-        EVW(16) = (int)(unsigned)(h >> 32);
+        ev_hash = h;
     }
 
     // state of body e at column c >= CS[e]-1 (position includes the correctOverlap offsets)
+    template <bool kEnd = false>   // kEnd: c = column 50 >= FL[e] of a live segment (the commit): no look-ups, no PRV case
     RGS_DEV void eval(int e, int c, T &px, T &py, T &vx, T &vy) const {
         const int j = c - s.I(S::CS + e);
-        if (j < 0) {
-            px = s.F(S::PRV + 4 * e); py = s.F(S::PRV + 4 * e + 1); vx = s.F(S::PRV + 4 * e + 2); vy = s.F(S::PRV + 4 * e + 3);
-            return;
+        if constexpr (!kEnd) {
+            if (j < 0) {
+                px = s.F(S::PRV + 4 * e); py = s.F(S::PRV + 4 * e + 1); vx = s.F(S::PRV + 4 * e + 2); vy = s.F(S::PRV + 4 * e + 3);
+                return;
+            }
         }
         const T spx = s.F(S::SP + 4 * e), spy = s.F(S::SP + 4 * e + 1), svx = s.F(S::SP + 4 * e + 2), svy = s.F(S::SP + 4 * e + 3);
         if (j == 0) { px = spx; py = spy; vx = svx; vy = svy; return; }
@@ -312,7 +315,8 @@ struct LaneGame {
         const T g = gk.g, k = gk.k, tj = P.d.dt_col * T(j);
         const T wx = svx - ux, wy = svy - uy;
         T ox, oy;
-        off_at(e, c, ox, oy);
+        if constexpr (kEnd) { ox = s.F(S::OFF + 2 * e); oy = s.F(S::OFF + 2 * e + 1); }
+        else off_at(e, c, ox, oy);
         px = fm(wx, k, fm(ux, tj, spx)) + ox;
         py = fm(wy, k, fm(uy, tj, spy)) + oy;
         vx = fm(wx, g, ux);
@@ -1247,7 +1251,7 @@ struct LaneGame {
 #pragma unroll 1
         for (int e = 0; e < E; ++e) {
             T px, py, vx, vy;
-            eval(e, kGrid, px, py, vx, vy);
+            eval<true>(e, kGrid, px, py, vx, vy);
             s.F(S::SP + 4 * e) = px; s.F(S::SP + 4 * e + 1) = py; s.F(S::SP + 4 * e + 2) = vx; s.F(S::SP + 4 * e + 3) = vy;
         }
     }
@@ -1316,8 +1320,7 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
     for (int i = 0; i < RGS_N_EVENTS; ++i) G.EVW(i) = 0;
     {
         const unsigned long long h0 = (unsigned long long)gev[RGS_EV_HASH];
-        G.EVW(RGS_EV_HASH) = (int)(unsigned)h0;
-        G.EVW(16) = (int)(unsigned)(h0 >> 32);
+        G.ev_hash = h0;
     }
     double *dmg = A.damage + game * (NP * NP);
     long long live = gev[RGS_EV_LIVE_STEPS], loop_iters = gev[RGS_EV_LOOP_ITERS], decided = gev[RGS_EV_DECIDED_STEP];
@@ -1374,7 +1377,7 @@ RGS_DEV void rollout_lane_game(const FastParams<T> &P, const RunArgs &A, const L
         else if (i == RGS_EV_LOOP_ITERS) v = loop_iters;
         else if (i == RGS_EV_DECIDED_STEP) v = decided;
         else if (i == RGS_EV_HASH)
-            v = (long long)(((unsigned long long)(unsigned)G.EVW(16) << 32) | (unsigned)G.EVW(RGS_EV_HASH));
+            v = (long long)G.ev_hash;
         else v = gev[i] + (long long)G.EVW(i);
         gev[i] = v;
     }
