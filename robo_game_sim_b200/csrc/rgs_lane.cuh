@@ -181,6 +181,20 @@ template <typename T>
 RGS_DEV T skip_sqrt(T x) { return T(sqrt(x)); }
 #endif
 
+// v = *ptr if p (a PREDICATED load: no branch, no reconvergence region -- the track look-ups sit in every position
+// evaluation of the event path and are almost never taken; as branches they cost 15 % of the kernel, profiles/r02_ab_variants.md)
+#ifdef RGS_HOST_EMU
+template <typename T>
+inline void ld_if(bool p, const T *ptr, T &v) { if (p) v = *ptr; }
+#else
+RGS_DEV void ld_if(bool p, const float *ptr, float &v) {
+    asm("{ .reg .pred q; setp.ne.s32 q, %2, 0; @q ld.global.f32 %0, [%1]; }" : "+f"(v) : "l"(ptr), "r"((int)p));
+}
+RGS_DEV void ld_if(bool p, const double *ptr, double &v) {
+    asm("{ .reg .pred q; setp.ne.s32 q, %2, 0; @q ld.global.f64 %0, [%1]; }" : "+d"(v) : "l"(ptr), "r"((int)p));
+}
+#endif
+
 // broad-phase slack: the bounding intervals are evaluated with different roundings than the
 // column positions, so thresholds are inflated by a few hundred ulps of the arena size
 template <typename T> struct Slack;
@@ -254,7 +268,10 @@ struct LaneGame {
         const bool late = c >= s.I(S::FL + e);
         ox = late ? s.F(S::OFF + 2 * e) : T(0);
         oy = late ? s.F(S::OFF + 2 * e + 1) : T(0);
-        if (__builtin_expect(!late && c >= s.I(S::FF + e), 0)) { ox = s.TR(e, c, 0); oy = s.TR(e, c, 1); }
+        const bool mid = !late && c >= s.I(S::FF + e);
+        const T *tp = &s.TR(e, c, 0);
+        ld_if(mid, tp, ox);
+        ld_if(mid, tp + 1, oy);
     }
     RGS_DEV T off_at1(int e, int a, int c) const {
         if (c >= s.I(S::FL + e)) return s.F(S::OFF + 2 * e + a);
@@ -431,9 +448,10 @@ struct LaneGame {
     }
     // q and its velocity at column c >= cs (closed form from the segment start)
     RGS_DEV T axis_off(const Axis &A, int c) const {   // mirrored cumulative offset at column c
-        T o = c >= A.fl ? A.off_t : T(0);
-        if (__builtin_expect(c < A.fl && c >= A.ff, 0)) o = A.sgn * s.TR(A.e, c, A.ax);
-        return o;
+        T o = c >= A.fl ? A.off_t : T(0), t = T(0);
+        const bool mid = c < A.fl && c >= A.ff;
+        ld_if(mid, &s.TR(A.e, c, A.ax), t);
+        return mid ? A.sgn * t : o;
     }
     RGS_DEV void axis_at(const Axis &A, int c, T &q, T &v) const {
         const int j = c - A.cs;
@@ -540,37 +558,20 @@ struct LaneGame {
         g.otx = s.F(S::OFF + 2 * e); g.oty = s.F(S::OFF + 2 * e + 1);
         return g;
     }
-    RGS_DEV void pos_at(const PosSeg &g, int c, T &px, T &py) const {
-        const int j = c - g.cs;
-        if (j <= 0) {
-            const int w = j < 0 ? S::PRV : S::SP;
-            px = s.F(w + 4 * g.e); py = s.F(w + 4 * g.e + 1);
-            return;
-        }
-        const LaneGK<T> gk = tab->e[g.ty][j];
-        const T tj = P.d.dt_col * T(j);
-        const bool late = c >= g.fl;
-        T ox = late ? g.otx : T(0), oy = late ? g.oty : T(0);
-        if (__builtin_expect(!late && c >= g.ff, 0)) { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
-        px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + ox;
-        py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + oy;
-        if constexpr (kNoise)
-            if (g.ty == 0) { px += NZ(g.e, c, 0); py += NZ(g.e, c, 1); }
-    }
-
     // position and velocity at column c (velocity: same arithmetic as eval())
     RGS_DEV void posvel_at(const PosSeg &g, int c, T &px, T &py, T &vx, T &vy) const {
+        // c >= cs for every caller (a segment starts at the base of its event, and bases never decrease).  At c == cs the
+        // closed form gives the start position exactly (k_0 = 0) and the start velocity to one rounding, which only feeds
+        // the conservative column-skip bound: no special case, no branch
         const int j = c - g.cs;
-        if (j <= 0) {
-            const int w = j < 0 ? S::PRV : S::SP;
-            px = s.F(w + 4 * g.e); py = s.F(w + 4 * g.e + 1); vx = s.F(w + 4 * g.e + 2); vy = s.F(w + 4 * g.e + 3);
-            return;
-        }
         const LaneGK<T> gk = tab->e[g.ty][j];
         const T tj = P.d.dt_col * T(j);
         const bool late = c >= g.fl;
         T ox = late ? g.otx : T(0), oy = late ? g.oty : T(0);
-        if (__builtin_expect(!late && c >= g.ff, 0)) { ox = s.TR(g.e, c, 0); oy = s.TR(g.e, c, 1); }
+        const bool mid = !late && c >= g.ff;
+        const T *tp = &s.TR(g.e, c, 0);
+        ld_if(mid, tp, ox);
+        ld_if(mid, tp + 1, oy);
         px = fm(g.wx, gk.k, fm(g.ux, tj, g.spx)) + ox;
         py = fm(g.wy, gk.k, fm(g.uy, tj, g.spy)) + oy;
         vx = fm(g.wx, gk.g, g.ux);
