@@ -128,6 +128,10 @@ struct Bits {
         for (int k = 0; k < NW; ++k)
             if ((b >> 5) == k) w[k] |= 1u << (b & 31);
     }
+    RGS_DEV void set_if(bool p, int b) {   // straight-line form of `if (p) set(b)`
+#pragma unroll
+        for (int k = 0; k < NW; ++k) w[k] |= (p && (b >> 5) == k) ? 1u << (b & 31) : 0u;
+    }
     RGS_DEV bool any() const {
         unsigned a = 0u;
 #pragma unroll
@@ -395,10 +399,10 @@ struct LaneGame {
         const int ty = (e == PK);
         const T sl = Slack<T>::v;
         const T lx = P.lim_x[ty] - sl, ly = P.lim_y[ty] - sl;
-        if (s.F(S::BB + 4 * e + 3) >= ly) wb.set(4 * e + WALL_UP);
-        if (s.F(S::BB + 4 * e + 2) <= -ly) wb.set(4 * e + WALL_DOWN);
-        if (s.F(S::BB + 4 * e + 1) >= lx) wb.set(4 * e + WALL_RIGHT);
-        if (s.F(S::BB + 4 * e + 0) <= -lx) wb.set(4 * e + WALL_LEFT);
+        wb.set_if(s.F(S::BB + 4 * e + 3) >= ly, 4 * e + WALL_UP);
+        wb.set_if(s.F(S::BB + 4 * e + 2) <= -ly, 4 * e + WALL_DOWN);
+        wb.set_if(s.F(S::BB + 4 * e + 1) >= lx, 4 * e + WALL_RIGHT);
+        wb.set_if(s.F(S::BB + 4 * e + 0) <= -lx, 4 * e + WALL_LEFT);
     }
     // can the bounding intervals of a and b come within r_a + r_b of each other?
     RGS_DEV bool flag_pair(int a, int b) const {
@@ -415,12 +419,12 @@ struct LaneGame {
         const T sl = Slack<T>::v;
         const int te = (e == PK);
 #pragma unroll 1
-        for (int o = 0; o < E; ++o) {
-            if (o == e || o == skip) continue;
+        for (int o = 0; o < E; ++o) {   // straight-line body (o == e gives a meaningless index that is never set)
             const T gx = tmax(T(0), tmax(lx - s.F(S::BB + 4 * o + 1), s.F(S::BB + 4 * o) - hx));
             const T gy = tmax(T(0), tmax(ly - s.F(S::BB + 4 * o + 3), s.F(S::BB + 4 * o + 2) - hy));
             const T sg = P.d.sig[te][o == PK] + sl;
-            if (fm(gx, gx, gy * gy) <= sg * sg) pb.set(o < e ? pair_index(o, e) : pair_index(e, o));
+            const int a = o < e ? o : e, b = o < e ? e : o;
+            pb.set_if(o != e && o != skip && fm(gx, gx, gy * gy) <= sg * sg, pair_index(a, b));
         }
     }
 
@@ -481,12 +485,13 @@ struct LaneGame {
                 const bool falling = A.w0 > T(0);  // velocity decreases along the segment (concave q)
                 int lo = base + 1, hi = kGrid + 1;
 #pragma unroll 1
-                for (int it = 0; it < 6; ++it) {
+                for (int it = 0; it < 6; ++it) {   // straight-line body (a finished search re-evaluates a valid column)
                     const int mid = (lo + hi) >> 1;
-                    if (lo < hi) {
-                        axis_at(A, mid, q, v);
-                        if (q >= lim || (falling && v <= T(0))) hi = mid; else lo = mid + 1;
-                    }
+                    const bool open = lo < hi;
+                    axis_at(A, open ? mid : base, q, v);
+                    const bool left = q >= lim || (falling && v <= T(0));
+                    hi = (open && left) ? mid : hi;
+                    lo = (open && !left) ? mid + 1 : lo;
                 }
                 c0 = lo;
                 if (c0 > kGrid) return kGrid + 1;
@@ -602,15 +607,15 @@ struct LaneGame {
     RGS_DEV int free_columns(T dx, T dy, T dvx, T dvy, T ssq, T sig, T eps, T inv_h) const {
         const T sg = sig + Slack<T>::v;
         const T C = ssq - sg * sg;
-        if (!(C > T(0))) return 0;
         const T A = fm(dvx, dvx, dvy * dvy) - eps * eps;
         const T B = fm(dx, dvx, dy * dvy) - sg * eps;
         const T disc = fm(B, B, -(A * C));
-        if (disc < T(0)) return 64;
-        const T den = skip_sqrt(disc) - B;
-        if (!(den > T(0))) return 64;
-        const T cols = T(0.98) * C * inv_h / den;
-        return (int)tmin(cols, T(64));
+        const T den = skip_sqrt(tmax(disc, T(0))) - B;
+        // straight-line (selects, no early returns: every branch of the search loops is a reconvergence region)
+        const bool never = disc < T(0) || !(den > T(0));
+        const T cols = tmin(T(0.98) * C * inv_h / (never ? T(1) : den), T(64));
+        const int n = never ? 64 : (int)cols;
+        return C > T(0) ? n : 0;
     }
 
     // same for the pair (a, b); the time is symmetric in (a, b) as in the reference (:482-494).
@@ -1226,10 +1231,10 @@ struct LaneGame {
                     s.F(S::BB + 4 * e + 2 * a + 1) = lohi[2 * a + 1];
                 }
                 const T lx = P.lim_x[ty] - sl, ly = P.lim_y[ty] - sl;
-                if (lohi[3] >= ly) wb.set(4 * e + WALL_UP);
-                if (lohi[2] <= -ly) wb.set(4 * e + WALL_DOWN);
-                if (lohi[1] >= lx) wb.set(4 * e + WALL_RIGHT);
-                if (lohi[0] <= -lx) wb.set(4 * e + WALL_LEFT);
+                wb.set_if(lohi[3] >= ly, 4 * e + WALL_UP);
+                wb.set_if(lohi[2] <= -ly, 4 * e + WALL_DOWN);
+                wb.set_if(lohi[1] >= lx, 4 * e + WALL_RIGHT);
+                wb.set_if(lohi[0] <= -lx, 4 * e + WALL_LEFT);
             }
             // flag_pair with the first body's interval held in registers
             const T sgpp = P.d.sig[0][0] + sl, sgpk = P.d.sig[0][1] + sl;
@@ -1242,7 +1247,7 @@ struct LaneGame {
                 for (int b = a + 1; b < E; ++b, ++pidx) {
                     const T gx = tmax(T(0), tmax(alx - s.F(S::BB + 4 * b + 1), s.F(S::BB + 4 * b) - ahx));
                     const T gy = tmax(T(0), tmax(aly - s.F(S::BB + 4 * b + 3), s.F(S::BB + 4 * b + 2) - ahy));
-                    if (fm(gx, gx, gy * gy) <= (b == PK ? thr_pk : thr_pp)) pb.set(pidx);
+                    pb.set_if(fm(gx, gx, gy * gy) <= (b == PK ? thr_pk : thr_pp), pidx);
                 }
             }
         }
