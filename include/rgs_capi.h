@@ -213,6 +213,32 @@ int rgs_write_logs(const double *h_traj, int64_t n_games, int64_t n_rec, int32_t
 int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_actions, int64_t n_act, int64_t hold,
                        int64_t n_steps, double *h_state, int64_t *h_events, int64_t *h_stats, void *stream);
 
+/* Allocation-free rollout.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops such as the K3 sampler tick,
+ * harnesses that forbid it).  It is rgs_batch_run without the batch object: the fp32 throughput kernel (K2, one lane
+ * per game) on n_games 2v2 games whose records the CALLER holds, with the kernel's per-lane scratch (correctOverlap
+ * tracks, event counters, jam snapshot) in a file-scope static __device__ array of the library instead of a
+ * cudaMalloc'ed buffer.  The call makes no cudaMalloc / cudaFree / allocating library call, on any invocation.
+ *   p          mode must be RGS_MODE_FAST_F32, players_per_team 2, noise 0 (RGS_EUNSUPPORTED otherwise)
+ *   n_games    0 .. RGS_NOALLOC_MAX_GAMES; more is rejected with RGS_EINVAL and a message naming the limit.  The
+ *              static array is RGS_NOALLOC_MAX_GAMES x 2708 B = 11.1 MB; every GPU that loads the library holds it
+ *              until the process exits
+ *   d_state    [n_games, 22] doubles, in: state before the first step, out: state after the last (in place)
+ *   d_clock    [n_games] doubles, in / out (the reference's t_)
+ *   d_damage   [n_games, 16] doubles, in / out (accumulated onto)
+ *   d_events   [n_games, RGS_N_EVENTS] int64, in / out: counters accumulated onto, the hash carried on (zero them
+ *              for a fresh run)
+ *   d_actions, n_act, hold, act_game_stride, n_steps: as rgs_batch_run, float records
+ * Asynchronous on `stream`.  ALL calls on a device share the one array: nothing in it has to start at zero (each
+ * lane re-initialises the words it reads before its game starts, so a call never sees the previous call's
+ * contents), but two calls that OVERLAP on the GPU (different streams, or graph branches without a dependency) race
+ * on it and corrupt each other -- order them on one stream or with an event.  The first call on a device looks the
+ * array's address up (cudaGetSymbolAddress) and loads the kernel; make that call outside graph capture. */
+#define RGS_NOALLOC_MAX_GAMES 4096
+int rgs_rollout_noalloc(int device, const rgs_params *p, int64_t n_games, double *d_state, double *d_clock,
+                        double *d_damage, int64_t *d_events, const float *d_actions, int64_t n_act, int64_t hold,
+                        int64_t act_game_stride, int64_t n_steps, void *stream);
+
 /* Batch-of-one convenience used by the drop-in class robo_game_py.GameSim
  * (replaces reference src/RoboGamePy.cpp:15-24 one to one). */
 typedef struct rgs_single rgs_single;

@@ -12,6 +12,7 @@ LIB_PATH = os.environ.get("RGS_B200_LIB") or os.path.join(_HERE, "librgs_b200.so
 RGS_OK, RGS_EINVAL, RGS_ECUDA, RGS_ENOMEM, RGS_EUNSUPPORTED = 0, -1, -2, -3, -4
 MODE_EXACT_F64, MODE_FAST_F32, MODE_FAST_F64 = 64, 32, 65
 N_EVENTS, N_STATS, MAX_TEAM = 16, 96, 7
+NOALLOC_MAX_GAMES = 4096   # RGS_NOALLOC_MAX_GAMES: rgs_rollout_noalloc's static scratch array
 
 EV_NAMES = ["goals_a", "goals_b", "wall_up", "wall_down", "wall_right", "wall_left", "player_player", "player_puck",
             "discarded", "loop_iters", "live_steps", "decided_step", "counter_limit", "base_clamp", "hash",
@@ -61,6 +62,7 @@ SIGNATURES = {
     "rgs_measure_peak": (C.c_int, [C.c_int, _i32, C.POINTER(_dbl)]),
     "rgs_write_logs": (C.c_int, [_vp, _i64, _i64, _i32, _vp, C.c_char_p, _i64, _i32, _i32]),
     "rgs_batch_run_host": (C.c_int, [_vp, _vp, _vp, _i64, _i64, _i64, _vp, _vp, _vp, _vp]),
+    "rgs_rollout_noalloc": (C.c_int, [C.c_int, _PP, _i64, _vp, _vp, _vp, _vp, _vp, _i64, _i64, _i64, _i64, _vp]),
     "rgs_single_create": (C.c_int, [C.POINTER(_vp), C.c_int]),
     "rgs_single_destroy": (C.c_int, [_vp]),
     "rgs_single_reset": (C.c_int, [_vp, _dbl, _i32, C.POINTER(_dbl), _dbl, _i32, C.c_char_p, _i32, _dbl, _dbl, _dbl,

@@ -186,6 +186,15 @@ int check_run_args(rgs_batch *b, int64_t n_act, int64_t hold, int64_t n_steps, i
 
 }  // namespace
 
+// hooks for entry points that live in other translation units (rgs_noalloc.cu): the same argument checks, the same
+// thread-local rgs_last_error() message and the same launch counter as the entry points of this file
+namespace rgs {
+int capi_check_params(const rgs_params *p) { return check_params(p); }
+int capi_fail(int code, const char *msg) { return fail(code, "%s", msg); }
+int capi_cuda_fail(cudaError_t e, const char *what) { return cuda_fail(e, what); }
+void capi_count_launches(int n) { g_launches.fetch_add(n); }
+}  // namespace rgs
+
 extern "C" {
 
 void rgs_default_params(rgs_params *p) {

@@ -36,4 +36,10 @@ cudaError_t launch_synth(uint64_t seed, int64_t first_game, int64_t n, int n_tea
 // FMA-chain micro-benchmark: the measured FP32 / FP64 issue peak used as the roofline denominator
 cudaError_t measure_fma_peak(int fp64, int sm_count, double *tflops);
 
+// rgs_capi.cu's argument check, error message (rgs_last_error) and launch counter, for entry points in other files
+int capi_check_params(const rgs_params *p);
+int capi_fail(int code, const char *msg);
+int capi_cuda_fail(cudaError_t e, const char *what);
+void capi_count_launches(int n);
+
 }  // namespace rgs
