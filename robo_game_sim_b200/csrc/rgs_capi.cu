@@ -489,7 +489,10 @@ int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_acti
     // Game-range chunks, double-buffered over two streams: the H2D copy of chunk c+1 and the D2H
     // copy of chunk c-1 overlap the rollout of chunk c (games are independent, so a chunk is
     // simply a contiguous slice of the batch).
-    int64_t n_chunks = N >= 65536 ? 8 : 1;
+#ifndef RGS_AB_CHUNKS
+#define RGS_AB_CHUNKS 8   // measured against 4 / 6 / 12 / 16 and a geometric plan: profiles/r02_ab_variants.md section 6
+#endif
+    int64_t n_chunks = N >= 65536 ? RGS_AB_CHUNKS : 1;
     const int64_t per = (N + n_chunks - 1) / (n_chunks > 0 ? n_chunks : 1);
     for (int64_t c = 0; c < n_chunks; ++c) {
         const int64_t g0 = c * per, g1 = (g0 + per < N) ? g0 + per : N;

@@ -1211,7 +1211,7 @@ struct LaneGame {
         pb.clear();
         {   // whole-step segments: update_bbox + flag_walls with cs = 0 and zero offsets, from registers
             const T trem = P.d.dt_col * T(kGrid), sl = Slack<T>::v;
-            const T gE[2] = {tab->e[0][kGrid].g, tab->e[1][kGrid].g};
+            const T gE0 = tab->e[0][kGrid].g, gE1 = tab->e[1][kGrid].g;   // (selected, not indexed: no local-memory array)
 #pragma unroll 1
             for (int e = 0; e < E; ++e) {
                 const int ty = (e == PK);
@@ -1223,7 +1223,7 @@ struct LaneGame {
                 for (int a = 0; a < 2; ++a) {
                     s.F(S::OFF + 2 * e + a) = T(0);
                     const T p = s.F(S::SP + 4 * e + a), v = s.F(S::SP + 4 * e + 2 + a), u = s.F(S::CMD + 2 * e + a);
-                    const T vE = fm(v - u, gE[ty], u);
+                    const T vE = fm(v - u, ty ? gE1 : gE0, u);
                     const T env = (kNoise && !ty) ? P.nz_env : T(0);
                     lohi[2 * a] = p + tmin(T(0), tmin(v, vE) * trem) - env;
                     lohi[2 * a + 1] = p + tmax(T(0), tmax(v, vE) * trem) + env;

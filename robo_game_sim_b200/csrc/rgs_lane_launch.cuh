@@ -65,7 +65,11 @@ constexpr int lane_big_threads() {
 #endif
 }
 
+#ifdef RGS_AB_SMALL_WARPS
+constexpr int kSmallWarpsPerSm = RGS_AB_SMALL_WARPS;
+#else
 constexpr int kSmallWarpsPerSm = 7;   // one-warp CTAs per SM aimed at by the small-batch path (see launch_lane_nt)
+#endif
 
 template <typename T, int NT, int kThreads, bool kPolicy, bool kNoise>
 static cudaError_t lane_resident_ctas(int lanes, int *per_sm) {
