@@ -122,6 +122,13 @@ int rgs_batch_reset(rgs_batch *b, const double *d_x0_ball, int64_t x0_stride, co
 int rgs_batch_run(rgs_batch *b, const void *d_actions, int64_t n_act, int64_t hold, int64_t act_game_stride,
                   int64_t n_steps, int64_t log_stride, double *d_traj, void *stream);
 
+/* Layout of the d_traj tensor the run entry points fill (no reference counterpart: the reference logs one game to one
+ * file, src/GameSim.cpp:161-170).  0 = records (default): [n_games, n_rec, TREC], a game's records contiguous -- the
+ * layout rgs_write_logs reads.  1 = field-major (SoA): [n_rec, TREC, n_games], the same field of consecutive games
+ * contiguous, so the 32 games of a warp store whole 32-byte sectors (K2: every-step logging costs 4x fewer memory
+ * transactions; profiles/r02_ab_variants.md section 7).  Applies to the following rgs_batch_run* calls. */
+int rgs_batch_set_traj_layout(rgs_batch *b, int32_t layout);
+
 /* Same, with the synthetic S0 action generator evaluated on chip (no action tensor in HBM):
  * player commands ~ U(-u_max,u_max)^2 redrawn every `hold` steps from Philox4x32-10 keyed by
  * (seed, first_game + g, step0/hold + k/hold); identical to rgs_synth_actions' output. */

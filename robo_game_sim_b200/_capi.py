@@ -49,6 +49,7 @@ SIGNATURES = {
     "rgs_batch_destroy": (C.c_int, [_vp]),
     "rgs_batch_set_params": (C.c_int, [_vp, _PP]),
     "rgs_batch_set_game_offset": (C.c_int, [_vp, _i64]),
+    "rgs_batch_set_traj_layout": (C.c_int, [_vp, _i32]),
     "rgs_batch_reset": (C.c_int, [_vp, _vp, _i64, _vp, _vp]),
     "rgs_batch_run": (C.c_int, [_vp, _vp, _i64, _i64, _i64, _i64, _i64, _vp, _vp]),
     "rgs_batch_run_synth": (C.c_int, [_vp, _u64, _i64, _i64, _i64, _dbl, _i64, _i64, _vp, _vp]),

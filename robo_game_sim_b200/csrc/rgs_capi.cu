@@ -80,6 +80,7 @@ struct rgs_batch {
     size_t lane_scratch_cap[3] = {0, 0, 0};
     size_t lane_scratch_need[2] = {0, 0};  // [noise-free, noise] kernels, queried on first use
     int64_t game_offset = 0;               // global index of game 0 (keys the process-noise streams)
+    int traj_layout = 0;                   // 0 records [N, n_rec, TREC], 1 field-major [n_rec, TREC, N] (rgs_batch_set_traj_layout)
     // staging for rgs_batch_run_host
     void *stage_actions = nullptr;
     size_t stage_actions_bytes = 0;
@@ -121,7 +122,13 @@ int run_range(rgs_batch *b, int64_t g0, int64_t g1, const void *d_actions, int64
     A.n_steps = n_steps;
     A.log_stride = log_stride;
     A.traj_recs = log_stride > 0 ? n_steps / log_stride : 0;
-    A.traj = d_traj ? d_traj + g0 * (n_steps / (log_stride > 0 ? log_stride : 1)) * (1 + b->srec + np * np) : nullptr;
+    if (b->traj_layout == 0) {
+        A.traj_field_stride = 1;
+        A.traj = d_traj ? d_traj + g0 * A.traj_recs * (1 + b->srec + np * np) : nullptr;
+    } else {   // field-major: the kernel indexes by the game's position in [g0, g1), so the base moves by g0 games
+        A.traj_field_stride = b->n_games;
+        A.traj = d_traj ? d_traj + g0 : nullptr;
+    }
     A.synth = synth;
     A.seed = seed;
     A.first_game = first_game + g0;
@@ -387,6 +394,13 @@ void rgs_default_policy(rgs_policy *pol) {
     pol->sweeps = 8;
     pol->kind = 0;
     pol->reserved = 0;
+}
+
+int rgs_batch_set_traj_layout(rgs_batch *b, int32_t layout) {
+    if (!b) return fail(RGS_EINVAL, "batch is NULL");
+    if (layout != 0 && layout != 1) return fail(RGS_EINVAL, "trajectory layout must be 0 (records) or 1 (field-major)");
+    b->traj_layout = layout;
+    return RGS_OK;
 }
 
 int rgs_batch_run_policy(rgs_batch *b, const rgs_policy *pol, int64_t n_steps, int64_t log_stride, double *d_traj,

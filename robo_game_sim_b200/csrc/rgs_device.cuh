@@ -73,6 +73,10 @@ struct RunArgs {
     int64_t n_steps, log_stride;
     double *traj;
     int64_t traj_recs;  // trajectory records per game = n_steps / log_stride (0 when not logging)
+    // trajectory layout: field f of record r of game g is traj[(g * traj_recs + r) * TREC + f] (records, the default:
+    // traj_field_stride = 1) or traj[(r * TREC + f) * traj_field_stride + g] (field-major, traj_field_stride = the
+    // batch's game count: the 32 lanes of a warp -- 32 consecutive games -- store 256 contiguous bytes per field)
+    int64_t traj_field_stride;
     // command source: 0 the action tensor, 1 on-chip synthetic actions, 2 the on-device policy `pol` (K2 lane kernel)
     int synth;
     uint64_t seed;

@@ -1272,23 +1272,52 @@ struct LaneGame {
 #else
 #define RGS_DEV_CALLED __device__ __noinline__
 #endif
-template <typename T, int NT>
-RGS_DEV_CALLED void write_traj_lane(const RunArgs &A, const LaneScratch<T, NT> s, int64_t game, int64_t rec_idx, double t_clock,
-                                    double sa, double sb) {
+template <typename T, int NT, bool kFieldMajor>
+RGS_DEV_CALLED void write_traj_lane_as(const RunArgs &A, const LaneScratch<T, NT> s, int64_t game, int64_t rec_idx, double t_clock,
+                                       double sa, double sb) {
     constexpr int E = 2 * NT + 1, PK = 2 * NT, SREC = 2 + 4 * E, NP = 2 * NT, TREC = 1 + SREC + NP * NP;
     using S = LaneScratch<T, NT>;
-    double *rec = A.traj + (game * A.traj_recs + rec_idx) * TREC;   // record rec_idx of this game (no 64-bit divisions here)
+    // record rec_idx of this game (no 64-bit divisions here); fs = distance between two fields of a record:
+    // 1 in the records layout (compile-time, so the field offsets fold into the store instructions), the batch's game
+    // count in the field-major layout (the 32 lanes of a warp then store 256 contiguous bytes per field)
+    const int64_t fs = kFieldMajor ? A.traj_field_stride : 1;
+    double *rec = kFieldMajor ? A.traj + rec_idx * TREC * fs + game : A.traj + (game * A.traj_recs + rec_idx) * TREC;
+    // The damage record comes from global memory: its loads are issued FIRST, a block of 16 doubles at a time, and
+    // consumed after the header and state stores, so the lane waits for one round trip per block at most (a rolled
+    // load-store loop cost the every-step logging run 29 % of its throughput).  The damage record is 16-byte aligned.
+    struct alignas(16) D2 { double x, y; };   // one 128-bit load
+    const D2 *dsrc = reinterpret_cast<const D2 *>(A.damage + game * (NP * NP));
+    double *dst = rec + (1 + SREC) * fs;
+    constexpr int kPairs = NP * NP / 2, kBlock = kPairs < 8 ? kPairs : 8;
+    D2 v[kBlock];
+#pragma unroll
+    for (int i = 0; i < kBlock; ++i) v[i] = dsrc[i];
     rec[0] = t_clock;
-    rec[1] = sa;
-    rec[2] = sb;
+    rec[fs] = sa;
+    rec[2 * fs] = sb;
 #pragma unroll 1
     for (int slot = 0; slot < E; ++slot) {
         const int e = slot == 0 ? PK : slot - 1;
-#pragma unroll 1
-        for (int c = 0; c < 4; ++c) rec[3 + 4 * slot + c] = (double)s.F(S::SP + 4 * e + c);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) rec[(3 + 4 * slot + c) * fs] = (double)s.F(S::SP + 4 * e + c);
     }
 #pragma unroll 1
-    for (int d = 0; d < NP * NP; ++d) rec[1 + SREC + d] = A.damage[game * (NP * NP) + d];
+    for (int d0 = 0;;) {
+#pragma unroll
+        for (int i = 0; i < kBlock; ++i)
+            if (d0 + i < kPairs) { dst[2 * (d0 + i) * fs] = v[i].x; dst[(2 * (d0 + i) + 1) * fs] = v[i].y; }
+        d0 += kBlock;
+        if (d0 >= kPairs) break;
+#pragma unroll
+        for (int i = 0; i < kBlock; ++i)
+            if (d0 + i < kPairs) v[i] = dsrc[d0 + i];
+    }
+}
+template <typename T, int NT>
+RGS_DEV void write_traj_lane(const RunArgs &A, const LaneScratch<T, NT> &s, int64_t game, int64_t rec_idx, double t_clock,
+                             double sa, double sb) {
+    if (A.traj_field_stride > 1) write_traj_lane_as<T, NT, true>(A, s, game, rec_idx, t_clock, sa, sb);
+    else write_traj_lane_as<T, NT, false>(A, s, game, rec_idx, t_clock, sa, sb);
 }
 
 // all n_steps of ONE game (the body of a lane).  The game lives in the lane's scratch record (shared memory)

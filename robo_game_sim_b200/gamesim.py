@@ -190,10 +190,25 @@ class BatchedGameSim:
         return self
 
     # ---- n_steps x GameSim::run for the whole batch, one fused launch ----
-    def run(self, actions, n_steps=None, hold=1, log_stride=0):
+    def _traj_tensor(self, n_steps, log_stride, traj_layout):
+        """the trajectory tensor of a run with log_stride > 0 and its device pointer; selects the layout for the call"""
+        if traj_layout not in ("records", "field_major"):
+            raise ValueError(f"traj_layout must be 'records' or 'field_major' (got {traj_layout!r})")
+        if not log_stride:
+            return None, None
+        torch = self._torch
+        n_rec, trec = int(n_steps) // int(log_stride), 1 + self.state_size + 4 * self.n_team * self.n_team
+        shape = (self.n_games, n_rec, trec) if traj_layout == "records" else (n_rec, trec, self.n_games)
+        _capi.check(self._lib.rgs_batch_set_traj_layout(self._h, 0 if traj_layout == "records" else 1))
+        traj = torch.empty(shape, dtype=torch.float64, device=self.device)
+        return traj, traj.data_ptr()
+
+    def run(self, actions, n_steps=None, hold=1, log_stride=0, traj_layout="records"):
         """actions: [N, n_act, 2n, 2] per-game or [n_act, 2n, 2] shared; step k uses action
-        min(k // hold, n_act-1).  Returns the trajectory tensor [N, n_steps//log_stride, 1+S+(2n)^2]
-        when log_stride > 0, else None."""
+        min(k // hold, n_act-1).  Returns the trajectory tensor when log_stride > 0, else None:
+        traj_layout "records" -> [N, n_steps//log_stride, 1+S+(2n)^2] (what write_logs reads), "field_major" ->
+        [n_steps//log_stride, 1+S+(2n)^2, N] (coalesced stores: the layout for every-step logging of large batches;
+        traj.permute(2, 0, 1) is the records view)."""
         torch = self._torch
         a = self._dev_tensor(actions, self.action_dtype, "actions")
         np2 = 2 * self.n_team
@@ -206,30 +221,21 @@ class BatchedGameSim:
                              f"got {tuple(a.shape)}")
         if n_steps is None:
             n_steps = n_act * hold
-        traj, traj_ptr = None, None
-        if log_stride:
-            traj = torch.empty((self.n_games, n_steps // log_stride, 1 + self.state_size + np2 * np2),
-                               dtype=torch.float64, device=self.device)
-            traj_ptr = traj.data_ptr()
+        traj, traj_ptr = self._traj_tensor(n_steps, log_stride, traj_layout)
         _capi.check(self._lib.rgs_batch_run(self._h, a.data_ptr(), n_act, int(hold), stride, int(n_steps),
                                             int(log_stride), traj_ptr, self._stream()))
         self._keep = [a]
         return traj
 
-    def run_synth(self, seed, n_steps, hold=10, u_max=10.0, first_game=0, step0=0, log_stride=0):
+    def run_synth(self, seed, n_steps, hold=10, u_max=10.0, first_game=0, step0=0, log_stride=0, traj_layout="records"):
         """Same, with the synthetic S0 commands generated on chip (no action tensor in HBM)."""
         torch = self._torch
-        traj, traj_ptr = None, None
-        if log_stride:
-            np2 = 2 * self.n_team
-            traj = torch.empty((self.n_games, n_steps // log_stride, 1 + self.state_size + np2 * np2),
-                               dtype=torch.float64, device=self.device)
-            traj_ptr = traj.data_ptr()
+        traj, traj_ptr = self._traj_tensor(n_steps, log_stride, traj_layout)
         _capi.check(self._lib.rgs_batch_run_synth(self._h, int(seed), int(first_game), int(step0), int(hold),
                                                   float(u_max), int(n_steps), int(log_stride), traj_ptr, self._stream()))
         return traj
 
-    def run_policy(self, n_steps, log_stride=0, **policy):
+    def run_policy(self, n_steps, log_stride=0, traj_layout="records", **policy):
         """Closed loop on the on-device surrogate of the reference's baseline team (ClassicalTeam play logic and
         targets, closed-form tracking law; `cbf=1` adds the CBF.py barrier filter): the commands are computed from
         the state inside the kernel every step.  policy: kick_velocity, gain, input_limit, safety_radius,
@@ -242,12 +248,7 @@ class BatchedGameSim:
             if k not in dict(_capi.RgsPolicy._fields_):
                 raise TypeError(f"unknown policy field {k!r}")
             setattr(pol, k, v)
-        traj, traj_ptr = None, None
-        if log_stride:
-            np2 = 2 * self.n_team
-            traj = torch.empty((self.n_games, n_steps // log_stride, 1 + self.state_size + np2 * np2),
-                               dtype=torch.float64, device=self.device)
-            traj_ptr = traj.data_ptr()
+        traj, traj_ptr = self._traj_tensor(n_steps, log_stride, traj_layout)
         _capi.check(self._lib.rgs_batch_run_policy(self._h, C.byref(pol), int(n_steps), int(log_stride), traj_ptr,
                                                    self._stream()))
         return traj

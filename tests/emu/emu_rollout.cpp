@@ -87,6 +87,7 @@ extern "C" int emu_rollout(const rgs_params *p, int64_t n_games, double *state, 
     A.n_steps = n_steps;
     A.log_stride = log_stride;
     A.traj_recs = log_stride > 0 ? n_steps / log_stride : 0;
+    A.traj_field_stride = 1;   // records layout
     A.traj = traj;
     A.synth = synth;
     A.seed = seed;

@@ -520,6 +520,33 @@ def test_batched_log_writer_matches_reference_files(rgs, tmp_path):
         sim.write_logs(traj, str(tmp_path / "no_placeholder.log"))
 
 
+@pytest.mark.parametrize("mode", ["fast", "fast64", "exact"])
+def test_trajectory_field_major_layout_equals_records(rgs, mode):
+    """rgs_batch_set_traj_layout: the field-major (SoA) trajectory tensor [n_rec, 39, N] of a run holds exactly the
+    records tensor [N, n_rec, 39] (ragged batch: 1 237 games is neither a multiple of 32 nor of 128; some games decide
+    early, so the frozen-record path is covered; strides 1 and 4; also the on-chip command generator's entry point)."""
+    n, steps, hold = 1237, 48, 10
+    x0, acts = rgs.synth_inputs(n, 5, seed=21)
+    for stride in (1, 4):
+        sims = [rgs.BatchedGameSim(n, mode=mode, winning_score=1) for _ in range(2)]
+        out = []
+        for sim, layout in zip(sims, ("records", "field_major")):
+            sim.reset(x0_ball=x0)
+            out.append(sim.run(acts.to(sim.action_dtype), n_steps=steps, hold=hold, log_stride=stride, traj_layout=layout))
+        assert out[0].shape == (n, steps // stride, 39) and out[1].shape == (steps // stride, 39, n)
+        assert torch.equal(out[1].permute(2, 0, 1), out[0])
+        assert torch.equal(sims[0].state(), sims[1].state())
+        assert int((sims[0].state()[:, :2].sum(1) >= 1).sum()) > 0    # some games were decided and frozen
+        # the layout is a property of the call: the same batch object switches back
+        sims[1].reset(x0_ball=x0)
+        back = sims[1].run_synth(3, steps, hold=hold, log_stride=stride)
+        sims[0].reset(x0_ball=x0)
+        fm = sims[0].run_synth(3, steps, hold=hold, log_stride=stride, traj_layout="field_major")
+        assert torch.equal(fm.permute(2, 0, 1), back)
+    with pytest.raises(ValueError):
+        sims[0].run(acts.to(sims[0].action_dtype), n_steps=steps, hold=hold, log_stride=1, traj_layout="soa")
+
+
 def test_damage_statistics_on_device(rgs):
     """K4 sums the damage matrix over the batch in fixed point (one integer all-reduce vector): equal to the sum of
     the per-game matrices to the fixed-point resolution, in exact and fast mode."""

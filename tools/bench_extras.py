@@ -7,7 +7,8 @@ bench.py calls measure_extras() on rank 0 at N = 1 and carries the result in the
   configs.sampler_tick_ms  BASELINE configs[4]: 4096 candidates x 50 steps from one shared state (reset_shared +
                          rollout + terminal cost / arg-min + 16-byte D2H), latency per controller tick
   configs.logging        fp32 rollout with a trajectory record written every 1 / 10 steps: game-steps/s and achieved
-                         HBM GB/s of the trajectory writes (north star: "achieved HBM GB/s on logging runs")
+                         HBM GB/s of the trajectory writes (north star: "achieved HBM GB/s on logging runs"); every
+                         step also in the field-major (SoA) trajectory layout
   latency.single_step_us BASELINE configs[0]: the drop-in GameSim (batch of one through rgs_single_run) over a
                          2000-step game (py/run_sim.py: T = 100 s), microseconds per run() call
 
@@ -95,21 +96,21 @@ def logging_runs(hbm_peak_gbs):
     out = {}
     sim = BatchedGameSim(n, mode="fast", winning_score=4)
     x0, acts = synth_inputs(n, steps // HOLD, seed=3, dtype=torch.float32)
-    for stride in (0, 10, 1):
+    for stride, layout in ((0, "records"), (10, "records"), (1, "records"), (1, "field_major")):
         traj = [None]
 
         def go():
             sim.reset(x0_ball=x0)
-            traj[0] = sim.run(acts, n_steps=steps, hold=HOLD, log_stride=stride)
+            traj[0] = sim.run(acts, n_steps=steps, hold=HOLD, log_stride=stride, traj_layout=layout)
 
         # reset is inside the timed call on purpose: the same region for every stride
         sec = timed(go)
         nbytes = 0 if traj[0] is None else traj[0].numel() * 8
-        out[f"log_stride_{stride}"] = {"game_steps_per_s": n * steps / sec, "ms": sec * 1e3, "traj_bytes": nbytes,
+        out[f"log_stride_{stride}" + ("_field_major" if layout != "records" else "")] = {"game_steps_per_s": n * steps / sec, "ms": sec * 1e3, "traj_bytes": nbytes,
                                        "traj_write_gbs": nbytes / sec / 1e9, "hbm_frac": nbytes / sec / 1e9 / hbm_peak_gbs}
         traj[0] = None
     base = out["log_stride_0"]["game_steps_per_s"]
-    for k in ("log_stride_10", "log_stride_1"):
+    for k in ("log_stride_10", "log_stride_1", "log_stride_1_field_major"):
         out[k]["loss_vs_no_log"] = 1.0 - out[k]["game_steps_per_s"] / base
     out["games"], out["steps"] = n, steps
     return out
