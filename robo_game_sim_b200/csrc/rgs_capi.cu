@@ -80,6 +80,7 @@ struct rgs_batch {
     size_t lane_scratch_cap[3] = {0, 0, 0};
     size_t lane_scratch_need[2] = {0, 0};  // [noise-free, noise] kernels, queried on first use
     int64_t game_offset = 0;               // global index of game 0 (keys the process-noise streams)
+    bool host_records = false;             // state / clock / damage / events live in mapped pinned HOST memory (rgs_single)
     int traj_layout = 0;                   // 0 records [N, n_rec, TREC], 1 field-major [n_rec, TREC, N] (rgs_batch_set_traj_layout)
     // staging for rgs_batch_run_host
     void *stage_actions = nullptr;
@@ -238,7 +239,13 @@ int rgs_device_count(int *out) {
     return RGS_OK;
 }
 
-int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_params *p) {
+}  // extern "C"
+
+namespace {
+// host_records: the game records are allocated in mapped pinned host memory instead of device memory.  The kernels
+// read and write them through the same (unified) addresses; the host reads results after a stream synchronise without
+// any cudaMemcpy.  Only the batch-of-one handle behind GameSim uses it: one launch per run() call and nothing else.
+int batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_params *p, bool host_records) {
     if (!out) return fail(RGS_EINVAL, "out is NULL");
     *out = nullptr;
     if (n_games < 0) return fail(RGS_EINVAL, "n_games must be >= 0");
@@ -264,10 +271,14 @@ int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_par
     cudaDeviceGetAttribute(&b->sm_count, cudaDevAttrMultiProcessorCount, device);
     const size_t n = (size_t)(n_games > 0 ? n_games : 1);
     cudaError_t err = cudaSuccess;
-    if (err == cudaSuccess) err = cudaMalloc(&b->state, n * b->srec * sizeof(double));
-    if (err == cudaSuccess) err = cudaMalloc(&b->clock, n * sizeof(double));
-    if (err == cudaSuccess) err = cudaMalloc(&b->damage, n * b->dmg_rec * sizeof(double));
-    if (err == cudaSuccess) err = cudaMalloc(&b->events, n * RGS_N_EVENTS * sizeof(long long));
+    b->host_records = host_records;
+    auto alloc = [&](void **ptr, size_t bytes) {
+        return host_records ? cudaHostAlloc(ptr, bytes, cudaHostAllocMapped) : cudaMalloc(ptr, bytes);
+    };
+    if (err == cudaSuccess) err = alloc(reinterpret_cast<void **>(&b->state), n * b->srec * sizeof(double));
+    if (err == cudaSuccess) err = alloc(reinterpret_cast<void **>(&b->clock), n * sizeof(double));
+    if (err == cudaSuccess) err = alloc(reinterpret_cast<void **>(&b->damage), n * b->dmg_rec * sizeof(double));
+    if (err == cudaSuccess) err = alloc(reinterpret_cast<void **>(&b->events), n * RGS_N_EVENTS * sizeof(long long));
     if (err == cudaSuccess) err = cudaMalloc(&b->stats, RGS_N_STATS * sizeof(long long));
     if (err != cudaSuccess) {
         rgs_batch_destroy(b);
@@ -284,15 +295,29 @@ int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_par
     }
     return RGS_OK;
 }
+}  // namespace
+
+extern "C" {
+
+int rgs_batch_create(rgs_batch **out, int device, int64_t n_games, const rgs_params *p) {
+    return batch_create(out, device, n_games, p, false);
+}
 
 int rgs_batch_destroy(rgs_batch *b) {
     if (!b) return RGS_OK;
     DeviceGuard guard(b->device);
     cudaDeviceSynchronize();
-    cudaFree(b->state);
-    cudaFree(b->clock);
-    cudaFree(b->damage);
-    cudaFree(b->events);
+    if (b->host_records) {
+        cudaFreeHost(b->state);
+        cudaFreeHost(b->clock);
+        cudaFreeHost(b->damage);
+        cudaFreeHost(b->events);
+    } else {
+        cudaFree(b->state);
+        cudaFree(b->clock);
+        cudaFree(b->damage);
+        cudaFree(b->events);
+    }
     cudaFree(b->stats);
     cudaFree(b->cost_scratch);
     for (int k = 0; k < 3; ++k) cudaFree(b->lane_scratch[k]);
@@ -610,8 +635,10 @@ struct rgs_single {
     rgs_batch *b = nullptr;        // the batch of the current game: b_exact (K1) or, with process noise, b_noise (K2 fp64)
     rgs_batch *b_exact = nullptr, *b_noise = nullptr;
     rgs_params p{};
-    double *d_act = nullptr, *d_x0 = nullptr;
-    double *h_pin = nullptr;  // pinned scratch: [0..21] state, [22..29] actions, [30] clock, [32..47] damage
+    // Zero-copy: the game records of the handle's batches and this scratch are mapped pinned host memory, so a run()
+    // call is ONE kernel launch and a stream synchronise -- the kernel fetches the eight commands and the record over
+    // PCIe and posts the new state back; no cudaMemcpy on the path (54 us -> see DESIGN.md section 6, latency row).
+    double *h_pin = nullptr;  // pinned, device-visible: [0..7] commands of the call, [8..11] x0_ball of reset()
     cudaStream_t stream = nullptr;
     FILE *log = nullptr;
     bool is_reset = false;
@@ -627,7 +654,7 @@ int rgs_single_create(rgs_single **out, int device) {
     if (!s) return fail(RGS_ENOMEM, "out of host memory");
     s->device = device;
     rgs_default_params(&s->p);
-    int rc = rgs_batch_create(&s->b_exact, device, 1, &s->p);
+    int rc = batch_create(&s->b_exact, device, 1, &s->p, true);
     if (rc != RGS_OK) { delete s; return rc; }
     s->b = s->b_exact;
     {   // the create-time reset ran on the legacy stream; this handle works on its own non-blocking stream
@@ -635,9 +662,7 @@ int rgs_single_create(rgs_single **out, int device) {
         cudaDeviceSynchronize();
     }
     DeviceGuard guard(device);
-    cudaError_t e = cudaMalloc(&s->d_act, 8 * sizeof(double));
-    if (e == cudaSuccess) e = cudaMalloc(&s->d_x0, 4 * sizeof(double));
-    if (e == cudaSuccess) e = cudaMallocHost(&s->h_pin, 64 * sizeof(double));
+    cudaError_t e = cudaHostAlloc(reinterpret_cast<void **>(&s->h_pin), 16 * sizeof(double), cudaHostAllocMapped);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
     if (e != cudaSuccess) { rgs_single_destroy(s); return cuda_fail(e, "rgs_single_create"); }
     *out = s;
@@ -649,8 +674,6 @@ int rgs_single_destroy(rgs_single *s) {
     {
         DeviceGuard guard(s->device);
         if (s->stream) { cudaStreamSynchronize(s->stream); cudaStreamDestroy(s->stream); }
-        cudaFree(s->d_act);
-        cudaFree(s->d_x0);
         if (s->h_pin) cudaFreeHost(s->h_pin);
     }
     if (s->log) fclose(s->log);
@@ -674,7 +697,7 @@ int rgs_single_reset(rgs_single *s, double dt, int32_t winning_score, const doub
     // fp64 with Philox process noise -- statistically, not bitwise, the reference's (its normal stream is libstdc++'s)
     p.mode = noise != 0.0 ? RGS_MODE_FAST_F64 : RGS_MODE_EXACT_F64;
     if (noise != 0.0 && !s->b_noise) {
-        int rcn = rgs_batch_create(&s->b_noise, s->device, 1, &p);
+        int rcn = batch_create(&s->b_noise, s->device, 1, &p, true);
         if (rcn != RGS_OK) return rcn;
         DeviceGuard guard(s->device);
         cudaDeviceSynchronize();
@@ -688,13 +711,11 @@ int rgs_single_reset(rgs_single *s, double dt, int32_t winning_score, const doub
     if (rc != RGS_OK) return rc;
     s->p = p;
     DeviceGuard guard(s->device);
-    std::memcpy(s->h_pin + 22, h_x0_ball, 4 * sizeof(double));
-    RGS_CUDA(cudaMemcpyAsync(s->d_x0, s->h_pin + 22, 4 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
-    rc = rgs_batch_reset(s->b, s->d_x0, 4, nullptr, s->stream);
+    std::memcpy(s->h_pin + 8, h_x0_ball, 4 * sizeof(double));
+    rc = rgs_batch_reset(s->b, s->h_pin + 8, 4, nullptr, s->stream);
     if (rc != RGS_OK) return rc;
-    RGS_CUDA(cudaMemcpyAsync(s->h_pin, s->b->state, 22 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
     RGS_CUDA(cudaStreamSynchronize(s->stream));
-    std::memcpy(s->h_state, s->h_pin, sizeof(s->h_state));
+    std::memcpy(s->h_state, s->b->state, sizeof(s->h_state));   // mapped pinned memory, written by the reset kernel
     if (h_out_state22) std::memcpy(h_out_state22, s->h_state, sizeof(s->h_state));
     // Logger::open (reference include/utils.h:54-59): close, then reopen truncating; a failed open is silent
     if (s->log) { fclose(s->log); s->log = nullptr; }
@@ -717,24 +738,18 @@ int rgs_single_run(rgs_single *s, const double *h_actions8, double *h_out_state2
     rgs_single_undecided(s, &live);
     if (live) {  // GameSim::run is a no-op once decided (reference src/GameSim.cpp:121-123)
         DeviceGuard guard(s->device);
-        std::memcpy(s->h_pin + 22, h_actions8, 8 * sizeof(double));
-        RGS_CUDA(cudaMemcpyAsync(s->d_act, s->h_pin + 22, 8 * sizeof(double), cudaMemcpyHostToDevice, s->stream));
-        int rc = rgs_batch_run(s->b, s->d_act, 1, 1, 0, 1, 0, nullptr, s->stream);
+        std::memcpy(s->h_pin, h_actions8, 8 * sizeof(double));
+        int rc = rgs_batch_run(s->b, s->h_pin, 1, 1, 0, 1, 0, nullptr, s->stream);
         if (rc != RGS_OK) return rc;
-        RGS_CUDA(cudaMemcpyAsync(s->h_pin, s->b->state, 22 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
-        if (s->log) {
-            RGS_CUDA(cudaMemcpyAsync(s->h_pin + 30, s->b->clock, sizeof(double), cudaMemcpyDeviceToHost, s->stream));
-            RGS_CUDA(cudaMemcpyAsync(s->h_pin + 32, s->b->damage, 16 * sizeof(double), cudaMemcpyDeviceToHost, s->stream));
-        }
         RGS_CUDA(cudaStreamSynchronize(s->stream));
-        std::memcpy(s->h_state, s->h_pin, sizeof(s->h_state));
+        std::memcpy(s->h_state, s->b->state, sizeof(s->h_state));
         if (s->log) {
             // 29-double record (reference src/GameSim.cpp:161-170).  damage.row(k) is written by
             // include/utils.h:75 as 4 CONTIGUOUS doubles from &damage(k,0) of a column-major 4x4,
             // i.e. column-major linear indices k..k+3; reproduced so files are byte-identical.
             double rec[29];
-            const double *st = s->h_state, *dm = s->h_pin + 32;  // dm: (aggressor, victim) row-major
-            rec[0] = s->h_pin[30];
+            const double *st = s->h_state, *dm = s->b->damage;  // dm: (aggressor, victim) row-major
+            rec[0] = s->b->clock[0];
             rec[1] = st[0]; rec[2] = st[1];
             rec[3] = st[2]; rec[4] = st[3];
             rec[5] = st[6]; rec[6] = st[7];
@@ -756,15 +771,13 @@ int rgs_single_run(rgs_single *s, const double *h_actions8, double *h_out_state2
 
 int rgs_single_time(rgs_single *s, double *out_t) {
     if (!s || !out_t) return fail(RGS_EINVAL, "NULL argument");
-    DeviceGuard guard(s->device);
-    RGS_CUDA(cudaMemcpy(out_t, s->b->clock, sizeof(double), cudaMemcpyDeviceToHost));
+    *out_t = s->b->clock[0];   // mapped pinned memory; every call of this handle ends with a stream synchronise
     return RGS_OK;
 }
 
 int rgs_single_damage(rgs_single *s, double *h_out16) {
     if (!s || !h_out16) return fail(RGS_EINVAL, "NULL argument");
-    DeviceGuard guard(s->device);
-    RGS_CUDA(cudaMemcpy(h_out16, s->b->damage, 16 * sizeof(double), cudaMemcpyDeviceToHost));
+    std::memcpy(h_out16, s->b->damage, 16 * sizeof(double));
     return RGS_OK;
 }
 

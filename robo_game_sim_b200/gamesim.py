@@ -34,6 +34,11 @@ def _vec(x, n, name):
     return np.ascontiguousarray(a.reshape(n))
 
 
+def _flat(x):
+    t = type(x)
+    return t is tuple or t is list or (t is np.ndarray and x.ndim == 1)
+
+
 class GameSim:
     """Drop-in for robo_game_py.GameSim (one 2v2 game, fp64 event-exact kernel K1)."""
 
@@ -41,6 +46,10 @@ class GameSim:
         self._lib = _capi.load()
         self._h = C.c_void_p()
         _capi.check(self._lib.rgs_single_create(C.byref(self._h), int(device)))
+        # run() is called once per game-step by the reference's scripts: its argument and result buffers are made once
+        self._act = (C.c_double * 8)()
+        self._out = (C.c_double * 22)()
+        self._out_np = np.frombuffer(self._out, dtype=np.float64)
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -70,12 +79,21 @@ class GameSim:
 
     def run(self, vel_A1, vel_A2, vel_B1, vel_B2):
         """GameSim::run (reference src/GameSim.cpp:118-124): one game-step -> float64[22] copy."""
-        act = np.concatenate([_vec(vel_A1, 2, "vel_A1"), _vec(vel_A2, 2, "vel_A2"), _vec(vel_B1, 2, "vel_B1"),
-                              _vec(vel_B2, 2, "vel_B2")])
-        out = np.empty(22, dtype=np.float64)
-        _capi.check(self._lib.rgs_single_run(self._h, act.ctypes.data_as(C.POINTER(C.c_double)),
-                                             out.ctypes.data_as(C.POINTER(C.c_double))))
-        return out
+        a = self._act
+        try:    # the common case: four flat length-2 sequences of Python / numpy floats
+            if not (_flat(vel_A1) and _flat(vel_A2) and _flat(vel_B1) and _flat(vel_B2)):
+                raise TypeError
+            a[0], a[1] = vel_A1
+            a[2], a[3] = vel_A2
+            a[4], a[5] = vel_B1
+            a[6], a[7] = vel_B2
+        except (TypeError, ValueError):   # (2,1) / (1,2) arrays, other containers -- or a TypeError for the caller
+            a[:] = list(np.concatenate([_vec(vel_A1, 2, "vel_A1"), _vec(vel_A2, 2, "vel_A2"), _vec(vel_B1, 2, "vel_B1"),
+                                        _vec(vel_B2, 2, "vel_B2")]))
+        rc = self._lib.rgs_single_run(self._h, a, self._out)
+        if rc:
+            _capi.check(rc)
+        return self._out_np.copy()
 
     # --- not in the reference binding (its clock and damage only reach the log file) ---
     def time(self):
