@@ -179,6 +179,13 @@ int rgs_batch_terminal_cost(rgs_batch *b, const double *d_x_des, const double *d
 /* State / clock / damage / events of all games into caller-provided DEVICE buffers (any may be NULL). */
 int rgs_batch_get(rgs_batch *b, double *d_state, double *d_t, double *d_damage, int64_t *d_events, void *stream);
 
+/* The inverse of rgs_batch_get: overwrite the records of all games from caller buffers (device or host memory; any may
+ * be NULL = left as it is).  Together they checkpoint and resume a batch exactly -- clock, damage and event records
+ * included, which rgs_batch_reset(d_state0) zeroes (the reference has no checkpoint; its clock and damage only reach
+ * the log file, src/GameSim.cpp:161-170). */
+int rgs_batch_set(rgs_batch *b, const double *d_state, const double *d_t, const double *d_damage, const int64_t *d_events,
+                  void *stream);
+
 /* K4: reduce scores + event records of the whole batch into int64[RGS_N_STATS] on the device
  * (overwritten).  Multi-GPU callers sum these vectors with one NCCL all-reduce. */
 int rgs_batch_stats(rgs_batch *b, int64_t *d_stats, void *stream);

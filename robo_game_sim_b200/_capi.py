@@ -56,6 +56,7 @@ SIGNATURES = {
     "rgs_default_policy": (None, [C.POINTER(RgsPolicy)]),
     "rgs_batch_run_policy": (C.c_int, [_vp, C.POINTER(RgsPolicy), _i64, _i64, _vp, _vp]),
     "rgs_batch_get": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
+    "rgs_batch_set": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),
     "rgs_batch_stats": (C.c_int, [_vp, _vp, _vp]),
     "rgs_batch_reset_shared": (C.c_int, [_vp, _vp, _vp]),
     "rgs_batch_terminal_cost": (C.c_int, [_vp, _vp, _vp, _vp, _vp, _vp]),

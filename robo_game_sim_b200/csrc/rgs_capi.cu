@@ -457,6 +457,20 @@ int rgs_batch_get(rgs_batch *b, double *d_state, double *d_t, double *d_damage, 
     return RGS_OK;
 }
 
+int rgs_batch_set(rgs_batch *b, const double *d_state, const double *d_t, const double *d_damage, const int64_t *d_events,
+                  void *stream) {
+    if (!b) return fail(RGS_EINVAL, "batch is NULL");
+    if (b->n_games == 0) return RGS_OK;
+    DeviceGuard guard(b->device);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const size_t n = (size_t)b->n_games;
+    if (d_state) RGS_CUDA(cudaMemcpyAsync(b->state, d_state, n * b->srec * sizeof(double), cudaMemcpyDefault, s));
+    if (d_t) RGS_CUDA(cudaMemcpyAsync(b->clock, d_t, n * sizeof(double), cudaMemcpyDefault, s));
+    if (d_damage) RGS_CUDA(cudaMemcpyAsync(b->damage, d_damage, n * b->dmg_rec * sizeof(double), cudaMemcpyDefault, s));
+    if (d_events) RGS_CUDA(cudaMemcpyAsync(b->events, d_events, n * RGS_N_EVENTS * sizeof(long long), cudaMemcpyDefault, s));
+    return RGS_OK;
+}
+
 int rgs_batch_stats(rgs_batch *b, int64_t *d_stats, void *stream) {
     if (!b) return fail(RGS_EINVAL, "batch is NULL");
     if (!d_stats) return fail(RGS_EINVAL, "d_stats is NULL");

@@ -284,6 +284,33 @@ class BatchedGameSim:
                                             self._stream()))
         return out
 
+    def checkpoint(self):
+        """All game records of the batch as device tensors: dict(state, time, damage, events) -- restore() takes it."""
+        return {k: self._get(k) for k in ("state", "time", "damage", "events")}
+
+    def restore(self, state=None, time=None, damage=None, events=None):
+        """Overwrite the game records (rgs_batch_set): resumes a checkpoint exactly, clock, damage and event records
+        included (reset(state0=...) zeroes those).  Any argument may be None = left as it is."""
+        torch = self._torch
+        np2 = 2 * self.n_team
+        want = {"state": (state, (self.n_games, self.state_size), torch.float64), "time": (time, (self.n_games,), torch.float64),
+                "damage": (damage, (self.n_games, np2, np2), torch.float64),
+                "events": (events, (self.n_games, _capi.N_EVENTS), torch.int64)}
+        ptrs, keep = {}, []
+        for k, (x, shape, dt) in want.items():
+            if x is None:
+                ptrs[k] = None
+                continue
+            t = self._dev_tensor(x, dt, k)
+            if t.numel() != int(np.prod(shape)):
+                raise ValueError(f"{k} must have shape {shape}, got {tuple(t.shape)}")
+            ptrs[k] = t.data_ptr()
+            keep.append(t)
+        _capi.check(self._lib.rgs_batch_set(self._h, ptrs["state"], ptrs["time"], ptrs["damage"], ptrs["events"],
+                                            self._stream()))
+        self._keep = keep
+        return self
+
     def state(self):
         return self._get("state")
 

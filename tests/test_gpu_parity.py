@@ -547,6 +547,31 @@ def test_trajectory_field_major_layout_equals_records(rgs, mode):
         sims[0].run(acts.to(sims[0].action_dtype), n_steps=steps, hold=hold, log_stride=1, traj_layout="soa")
 
 
+@pytest.mark.parametrize("mode", ["exact", "fast"])
+def test_checkpoint_and_restore_resume_exactly(rgs, mode):
+    """rgs_batch_get / rgs_batch_set: a batch restored from a checkpoint into ANOTHER batch object and carried on gives
+    the bits of the uninterrupted run -- state, clock, damage and event records (hash included); reset(state0=...)
+    alone would have zeroed the last three."""
+    n, hold = 3000, 10
+    x0, acts = rgs.synth_inputs(n, 10, seed=5)
+    a = rgs.BatchedGameSim(n, mode=mode, winning_score=3)
+    acts = acts.to(a.action_dtype)
+    a.reset(x0_ball=x0)
+    a.run(acts, n_steps=100, hold=hold)
+    b = rgs.BatchedGameSim(n, mode=mode, winning_score=3)
+    b.reset(x0_ball=x0)
+    b.run(acts[:, :6], n_steps=60, hold=hold)
+    ck = b.checkpoint()
+    assert float(ck["time"].min()) > 0 and int(ck["events"][:, 2:8].sum()) > 0 and float(ck["damage"].sum()) > 0
+    c = rgs.BatchedGameSim(n, mode=mode, winning_score=3)
+    c.restore(**ck)
+    c.run(acts[:, 6:].contiguous(), n_steps=40, hold=hold)
+    for k, v in a.checkpoint().items():
+        assert torch.equal(v, c.checkpoint()[k]), k
+    with pytest.raises(ValueError):
+        c.restore(state=ck["state"][:10])
+
+
 def test_damage_statistics_on_device(rgs):
     """K4 sums the damage matrix over the batch in fixed point (one integer all-reduce vector): equal to the sum of
     the per-game matrices to the fixed-point resolution, in exact and fast mode."""
