@@ -691,8 +691,11 @@ struct LaneGame {
             T t;
             const int c = search_pair(a, b, base, t);
             if (c <= kGrid) {
-                if ((owners >> a) & 1u) fold(a, c, t, PAIR, b, fmask);
-                if ((owners >> b) & 1u) fold(b, c, t, PAIR, a, fmask);
+#pragma unroll 1
+                for (int k = 0; k < 2; ++k) {   // (rolled: one copy of fold)
+                    const int own = k == 0 ? a : b, oth = k == 0 ? b : a;
+                    if ((owners >> own) & 1u) fold(own, c, t, PAIR, oth, fmask);
+                }
             }
         }
     }
@@ -924,7 +927,6 @@ struct LaneGame {
             start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
             start_segment(ej, base, pjx, pjy, vjx, vjy, qjx, qjy, qvjx, qvjy);
             march_pair(ei, ej, base);
-            update_bbox(ej);
             rj = ej;
         } else {  // wall :300-343
             switch (ekind) {  // flip only while still moving into the wall :312-318
@@ -960,9 +962,8 @@ struct LaneGame {
             start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
             if (!is_goal) march_wall(ei, ekind, base);
         }
-        update_bbox(ei);
         hash_ev(live, ekind, ei, ej, goal);
-        return rj;
+        return rj;   // (the caller refreshes the bounding intervals of ei and rj: event_loop)
     }
 
     // ---- jammed steps ------------------------------------------------------------------------------------
@@ -1154,15 +1155,25 @@ struct LaneGame {
                     scored = true;
                 }
                 prune(qmask, ei, ej);  // :347-352
-                // re-scan the bodies involved (:355-357, :147): broad phase on their new segments
-                owners = 1u << ei;
-                flag_walls(ei, wb);
-                if (rj >= 0) {
-                    owners |= 1u << rj;
-                    flag_walls(rj, wb);
+                // re-scan the bodies involved (:355-357, :147): broad phase on their new segments.  Two rolled
+                // two-trip loops, so that the kernel holds ONE copy of update_bbox / flag_walls / reflag_pairs: the
+                // kernel is instruction-fetch-bound and its hot code sits just above the 32 KB instruction cache
+                // (about 3 % per 100 instructions of hot code, profiles/r02_ab_variants.md section 9)
+                owners = 0;
+#pragma unroll 1
+                for (int k = 0; k < 2; ++k) {
+                    const int e = k == 0 ? ei : rj;
+                    if (e < 0) break;
+                    owners |= 1u << e;
+                    update_bbox(e);
+                    flag_walls(e, wb);
                 }
-                reflag_pairs(ei, -1, pb);
-                if (rj >= 0) reflag_pairs(rj, ei, pb);
+#pragma unroll 1
+                for (int k = 0; k < 2; ++k) {
+                    const int e = k == 0 ? ei : rj;
+                    if (e < 0) break;
+                    reflag_pairs(e, k == 0 ? -1 : ei, pb);
+                }
                 ++counter;
             }
             if (qmask != 0) ev_add(RGS_EV_COUNTER_LIMIT);
