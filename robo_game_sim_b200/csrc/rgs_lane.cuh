@@ -220,6 +220,14 @@ struct LaneGame {
     // ABSOLUTE clock arithmetic (T[i] = t_ + dt_col_ i :201, t_col - t_ < dt_ :501, base_idx :237, dt_t :254):
     // for contacts resting on a grid time the rounding of t_ decides between two columns.
     static constexpr bool kAbsClock = sizeof(T) == 8;
+    // One inline copy of the post-event broad phase (update_bbox / flag_walls / reflag_pairs) and of fold, in rolled
+    // two-trip loops, instead of one copy per body of the event: the kernels of the small teams are bound by the
+    // fetch of a hot code just above the instruction cache (+3 - 5 % for 1v1 .. 4v4); for 7v7, whose code is far above it
+    // anyway, the rolled form costs 7 % (profiles/r02_ab_variants.md section 9).
+#ifndef RGS_AB_ONECOPY_MAXNT
+#define RGS_AB_ONECOPY_MAXNT 4
+#endif
+    static constexpr bool kOneCopy = NT <= RGS_AB_ONECOPY_MAXNT;
     mutable T t0 = T(0);
     mutable double tclk = 0.0;   // the game clock t_ at the start of the step (fp64, t_ += dt_ like the reference)
     RGS_DEV T col_time(int c) const {
@@ -691,10 +699,15 @@ struct LaneGame {
             T t;
             const int c = search_pair(a, b, base, t);
             if (c <= kGrid) {
+                if constexpr (kOneCopy) {
 #pragma unroll 1
-                for (int k = 0; k < 2; ++k) {   // (rolled: one copy of fold)
-                    const int own = k == 0 ? a : b, oth = k == 0 ? b : a;
-                    if ((owners >> own) & 1u) fold(own, c, t, PAIR, oth, fmask);
+                    for (int k = 0; k < 2; ++k) {   // (rolled: one copy of fold)
+                        const int own = k == 0 ? a : b, oth = k == 0 ? b : a;
+                        if ((owners >> own) & 1u) fold(own, c, t, PAIR, oth, fmask);
+                    }
+                } else {
+                    if ((owners >> a) & 1u) fold(a, c, t, PAIR, b, fmask);
+                    if ((owners >> b) & 1u) fold(b, c, t, PAIR, a, fmask);
                 }
             }
         }
@@ -927,6 +940,7 @@ struct LaneGame {
             start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
             start_segment(ej, base, pjx, pjy, vjx, vjy, qjx, qjy, qvjx, qvjy);
             march_pair(ei, ej, base);
+            if constexpr (!kOneCopy) update_bbox(ej);
             rj = ej;
         } else {  // wall :300-343
             switch (ekind) {  // flip only while still moving into the wall :312-318
@@ -962,8 +976,9 @@ struct LaneGame {
             start_segment(ei, base, pix, piy, vix, viy, qix, qiy, qvix, qviy);
             if (!is_goal) march_wall(ei, ekind, base);
         }
+        if constexpr (!kOneCopy) update_bbox(ei);   // (kOneCopy: the caller refreshes the bounding intervals, event_loop)
         hash_ev(live, ekind, ei, ej, goal);
-        return rj;   // (the caller refreshes the bounding intervals of ei and rj: event_loop)
+        return rj;
     }
 
     // ---- jammed steps ------------------------------------------------------------------------------------
@@ -1159,20 +1174,31 @@ struct LaneGame {
                 // two-trip loops, so that the kernel holds ONE copy of update_bbox / flag_walls / reflag_pairs: the
                 // kernel is instruction-fetch-bound and its hot code sits just above the 32 KB instruction cache
                 // (about 3 % per 100 instructions of hot code, profiles/r02_ab_variants.md section 9)
-                owners = 0;
+                if constexpr (kOneCopy) {
+                    owners = 0;
 #pragma unroll 1
-                for (int k = 0; k < 2; ++k) {
-                    const int e = k == 0 ? ei : rj;
-                    if (e < 0) break;
-                    owners |= 1u << e;
-                    update_bbox(e);
-                    flag_walls(e, wb);
-                }
+                    for (int k = 0; k < 2; ++k) {
+                        const int e = k == 0 ? ei : rj;
+                        if (e < 0) break;
+                        owners |= 1u << e;
+                        update_bbox(e);
+                        flag_walls(e, wb);
+                    }
 #pragma unroll 1
-                for (int k = 0; k < 2; ++k) {
-                    const int e = k == 0 ? ei : rj;
-                    if (e < 0) break;
-                    reflag_pairs(e, k == 0 ? -1 : ei, pb);
+                    for (int k = 0; k < 2; ++k) {
+                        const int e = k == 0 ? ei : rj;
+                        if (e < 0) break;
+                        reflag_pairs(e, k == 0 ? -1 : ei, pb);
+                    }
+                } else {
+                    owners = 1u << ei;
+                    flag_walls(ei, wb);
+                    if (rj >= 0) {
+                        owners |= 1u << rj;
+                        flag_walls(rj, wb);
+                    }
+                    reflag_pairs(ei, -1, pb);
+                    if (rj >= 0) reflag_pairs(rj, ei, pb);
                 }
                 ++counter;
             }
