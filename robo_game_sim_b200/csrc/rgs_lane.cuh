@@ -247,6 +247,27 @@ struct LaneGame {
     mutable long long nz_game = 0;        // global game index
     mutable unsigned nz_step = 0, nz_epoch = 0;
     mutable bool nz_on = false;           // false while a quiet step commits from the closed form
+    // Players whose noise path of the current segment exists.  Paths are generated LAZILY: a flagged step needs the
+    // path of a player only if a narrow-phase item or an event evaluates it between the step's ends; every other
+    // player gets the end of its path at the commit, drawn from the accumulated Gaussian like in a quiet step (the
+    // same distribution: the players' noises are independent).  Generating all 2n paths for every flagged step cost
+    // 50 Philox blocks per player and step.
+    mutable unsigned nz_have = 0;
+    RGS_DEV void ensure_path(int e) const {
+        if (e != PK && !((nz_have >> e) & 1u)) {
+            gen_noise_path(e, s.I(S::CS + e));   // (no event has touched e yet: its segment is the whole step, CS = 0)
+            nz_have |= 1u << e;
+        }
+    }
+    // end-of-step noise of player e from the accumulated Gaussian of the 50 sub-steps
+    RGS_DEV void add_end_noise(int e) const {
+        T g[4];
+        normals4<T>(P.seed_lo, P.seed_hi, nz_game, nz_step, (unsigned)e, g);
+        s.F(S::SP + 4 * e) += fm(P.nz_end[1], g[0], P.nz_end[2] * g[1]);
+        s.F(S::SP + 4 * e + 1) += fm(P.nz_end[1], g[2], P.nz_end[2] * g[3]);
+        s.F(S::SP + 4 * e + 2) += P.nz_end[0] * g[0];
+        s.F(S::SP + 4 * e + 3) += P.nz_end[0] * g[2];
+    }
     RGS_DEV T &NZ(int e, int c, int k) const { return s.trk[S::NZ0 + (e * kCols + c) * 4 + k]; }
     RGS_DEV void gen_noise_path(int e, int c0) const {
         T npx = T(0), npy = T(0), nvx = T(0), nvy = T(0);
@@ -351,7 +372,7 @@ struct LaneGame {
         vx = fm(wx, g, ux);
         vy = fm(wy, g, uy);
         if constexpr (kNoise)
-            if (nz_on && e != PK) { px += NZ(e, c, 0); py += NZ(e, c, 1); vx += NZ(e, c, 2); vy += NZ(e, c, 3); }
+            if (nz_on && ((nz_have >> e) & 1u)) { px += NZ(e, c, 0); py += NZ(e, c, 1); vx += NZ(e, c, 2); vy += NZ(e, c, 3); }
     }
 
     // start a new segment of body e at column c with state (px,py,vx,vy); prev = state at c-1
@@ -363,7 +384,7 @@ struct LaneGame {
         s.I(S::FL + e) = c;
         s.I(S::FF + e) = c;
         if constexpr (kNoise)
-            if (e != PK) gen_noise_path(e, c);
+            if (e != PK) { gen_noise_path(e, c); nz_have |= 1u << e; }
     }
 
     // bounding interval of body e over columns CS[e]..50 (monotone-velocity bound + offsets)
@@ -689,6 +710,7 @@ struct LaneGame {
         while ((bit = wb.pop()) >= 0) {
             const int a = bit >> 2, wk = bit & 3;
             T t;
+            if constexpr (kNoise) ensure_path(a);
             const int c = search_wall(a, wk, base, t);
             if (c <= kGrid) fold(a, c, t, wk, 15, fmask);
         }
@@ -697,6 +719,7 @@ struct LaneGame {
             int a, b;
             pair_decode(bit, a, b);
             T t;
+            if constexpr (kNoise) { ensure_path(a); ensure_path(b); }
             const int c = search_pair(a, b, base, t);
             if (c <= kGrid) {
                 if constexpr (kOneCopy) {
@@ -1214,7 +1237,8 @@ struct LaneGame {
         tclk = t_clock;
         Bits<4 * E> wb;
         Bits<NPAIR> pb;
-        step_head(wb, pb);
+        unsigned need;
+        step_head(wb, pb, need);
         if constexpr (kNoise) {
             nz_step = (unsigned)live;
             nz_epoch = 0;
@@ -1224,28 +1248,32 @@ struct LaneGame {
                 nz_on = false;
                 step_commit();
 #pragma unroll 1
-                for (int e = 0; e < NP; ++e) {
-                    T g[4];
-                    normals4<T>(P.seed_lo, P.seed_hi, nz_game, nz_step, (unsigned)e, g);
-                    s.F(S::SP + 4 * e) += fm(P.nz_end[1], g[0], P.nz_end[2] * g[1]);
-                    s.F(S::SP + 4 * e + 1) += fm(P.nz_end[1], g[2], P.nz_end[2] * g[3]);
-                    s.F(S::SP + 4 * e + 2) += P.nz_end[0] * g[0];
-                    s.F(S::SP + 4 * e + 3) += P.nz_end[0] * g[2];
-                }
+                for (int e = 0; e < NP; ++e) add_end_noise(e);
                 return 1;
             }
             nz_on = true;
+            nz_have = 0;
+            // the paths of the bodies of the flagged items, generated here with all the lanes of the warp together; a
+            // body that only gets involved later in the step gets its path then (ensure_path in run_items)
 #pragma unroll 1
-            for (int e = 0; e < NP; ++e) gen_noise_path(e, 0);
+            for (int e = 0; e < NP; ++e)
+                if ((need >> e) & 1u) ensure_path(e);
         }
         const int counter = event_loop(wb, pb, sa, sb, dmg, live);
         step_commit();
+        if constexpr (kNoise) {
+#pragma unroll 1
+            for (int e = 0; e < NP; ++e)
+                if (!((nz_have >> e) & 1u)) add_end_noise(e);   // players nothing evaluated inside the step
+        }
         return counter;
     }
     // whole-step segments of all bodies and their broad-phase flags
-    RGS_DEV void step_head(Bits<4 * E> &wb, Bits<NPAIR> &pb) const {
+    // need (noise kernels): the bodies of the flagged items -- their noise paths are generated up front, all lanes together
+    RGS_DEV void step_head(Bits<4 * E> &wb, Bits<NPAIR> &pb, unsigned &need) const {
         wb.clear();
         pb.clear();
+        need = 0u;
         {   // whole-step segments: update_bbox + flag_walls with cs = 0 and zero offsets, from registers
             const T trem = P.d.dt_col * T(kGrid), sl = Slack<T>::v;
             const T gE0 = tab->e[0][kGrid].g, gE1 = tab->e[1][kGrid].g;   // (selected, not indexed: no local-memory array)
@@ -1272,6 +1300,8 @@ struct LaneGame {
                 wb.set_if(lohi[2] <= -ly, 4 * e + WALL_DOWN);
                 wb.set_if(lohi[1] >= lx, 4 * e + WALL_RIGHT);
                 wb.set_if(lohi[0] <= -lx, 4 * e + WALL_LEFT);
+                if constexpr (kNoise)
+                    need |= (lohi[3] >= ly || lohi[2] <= -ly || lohi[1] >= lx || lohi[0] <= -lx) ? 1u << e : 0u;
             }
             // flag_pair with the first body's interval held in registers
             const T sgpp = P.d.sig[0][0] + sl, sgpk = P.d.sig[0][1] + sl;
@@ -1284,7 +1314,9 @@ struct LaneGame {
                 for (int b = a + 1; b < E; ++b, ++pidx) {
                     const T gx = tmax(T(0), tmax(alx - s.F(S::BB + 4 * b + 1), s.F(S::BB + 4 * b) - ahx));
                     const T gy = tmax(T(0), tmax(aly - s.F(S::BB + 4 * b + 3), s.F(S::BB + 4 * b + 2) - ahy));
-                    pb.set_if(fm(gx, gx, gy * gy) <= (b == PK ? thr_pk : thr_pp), pidx);
+                    const bool near = fm(gx, gx, gy * gy) <= (b == PK ? thr_pk : thr_pp);
+                    pb.set_if(near, pidx);
+                    if constexpr (kNoise) need |= near ? (1u << a) | (1u << b) : 0u;
                 }
             }
         }
