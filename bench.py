@@ -361,8 +361,8 @@ def main():
                "per_rank_host_gbs": [round((G * 4 * 8 + G * n_act * 8 * esz + G * 22 * 8 + G * 16 * 8) * reps / float(t.item()) / 1e9, 2)
                                      for t in rank_secs],
                "per_rank_pass_ms": [round(float(t.item()) / reps * 1e3, 2) for t in rank_secs], "numa": numa,
-               "api": "BatchedGameSim.run_host -> rgs_batch_run_host (pinned host buffers, 8 game-range chunks "
-                      "double-buffered over 2 streams)"}
+               "api": "BatchedGameSim.run_host -> rgs_batch_run_host (pinned host buffers, 6 game-range chunks of 2, 6, 8, 8, 6, "
+                      "2 thirty-seconds of the batch double-buffered over 2 streams)"}
 
     if rank != 0:
         if world > 1:

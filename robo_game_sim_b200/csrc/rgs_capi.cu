@@ -542,14 +542,33 @@ int rgs_batch_run_host(rgs_batch *b, const double *h_x0_ball, const void *h_acti
     // Game-range chunks, double-buffered over two streams: the H2D copy of chunk c+1 and the D2H
     // copy of chunk c-1 overlap the rollout of chunk c (games are independent, so a chunk is
     // simply a contiguous slice of the batch).
-#ifndef RGS_AB_CHUNKS
-#define RGS_AB_CHUNKS 8   // measured against 4 / 6 / 12 / 16 and a geometric plan: profiles/r02_ab_variants.md section 6
+    // What stays exposed is the H2D copy of the FIRST chunk and the D2H copy of the LAST one, so those two ends are
+    // cut finer than the middle (plan in 32nds of the batch; profiles/r02_ab_variants.md section 6).
+    // Measured (tools/ab_e2e.sh, 10^6 games x 200 steps): 8 equal chunks 66.4 - 66.7 ms per pass at N = 1 and
+    // 2.22e10 game-steps/s end to end on 8 GPUs; this plan 64.5 - 65.3 ms and 2.32e10 (98 % of the device-timed rate).
+    // Chunk sizes are also a matter of wave quantisation on the 75 776-lane resident grid (5/32 + 10/32 loses).
+#if defined(RGS_AB_PLAN) && RGS_AB_PLAN == 1
+    static const int kPlan[] = {4, 4, 4, 4, 4, 4, 4, 4};
+#else
+    static const int kPlan[] = {2, 6, 8, 8, 6, 2};
 #endif
-    int64_t n_chunks = N >= 65536 ? RGS_AB_CHUNKS : 1;
-    const int64_t per = (N + n_chunks - 1) / (n_chunks > 0 ? n_chunks : 1);
+    constexpr int kPlanLen = (int)(sizeof(kPlan) / sizeof(kPlan[0]));
+    int64_t bounds[kPlanLen + 1];
+    int64_t n_chunks = 1;
+    bounds[0] = 0;
+    bounds[1] = N;
+    if (N >= 65536) {
+        n_chunks = kPlanLen;
+        int acc = 0;
+        for (int c = 0; c < kPlanLen; ++c) {
+            acc += kPlan[c];
+            bounds[c + 1] = N / 32 * acc + (N % 32) * acc / 32;
+        }
+        bounds[kPlanLen] = N;
+    }
     for (int64_t c = 0; c < n_chunks; ++c) {
-        const int64_t g0 = c * per, g1 = (g0 + per < N) ? g0 + per : N;
-        if (g1 <= g0) break;
+        const int64_t g0 = bounds[c], g1 = bounds[c + 1];
+        if (g1 <= g0) continue;
         cudaStream_t s = b->streams[c & 1];
         const int64_t ng = g1 - g0;
         RGS_CUDA(cudaMemcpyAsync(static_cast<char *>(b->stage_actions) + (size_t)g0 * arec * esz,
