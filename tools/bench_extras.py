@@ -4,6 +4,7 @@ bench.py calls measure_extras() on rank 0 at N = 1 and carries the result in the
   modes.exact            K1 (fp64 event-exact parity mode), 2x10^5 S0 games x 200 steps, own FP64-issue roofline
   configs.nvn            BASELINE configs[3]: 4v4 and 7v7 team games, fp32 throughput kernel and fp64 exact kernel
   configs.collision_batch  BASELINE configs[2] size: the exact kernel on 10^5 games x 400 steps
+  configs.noise          the FAST kernels with process noise on (reset(noise = 0.05), reference src/GameSim.cpp:62-68), fp32 and fp64
   configs.sampler_tick_ms  BASELINE configs[4]: 4096 candidates x 50 steps from one shared state (reset_shared +
                          rollout + terminal cost / arg-min + 16-byte D2H), latency per controller tick
   configs.logging        fp32 rollout with a trajectory record written every 1 / 10 steps: game-steps/s and achieved
@@ -41,14 +42,16 @@ def timed(fn, reps=4):
     return float(np.median(ms[1:])) * 1e-3
 
 
-def rollout_rate(n_team, mode, n_games, steps, peak_tflops=None, reps=4):
-    sim = BatchedGameSim(n_games, mode=mode, players_per_team=n_team, winning_score=4)
+def rollout_rate(n_team, mode, n_games, steps, peak_tflops=None, reps=4, noise=0.0):
+    sim = BatchedGameSim(n_games, mode=mode, players_per_team=n_team, winning_score=4, noise=noise, seed=1)
     x0, acts = synth_inputs(n_games, steps // HOLD, seed=11, players_per_team=n_team, dtype=sim.action_dtype)
     sim.reset(x0_ball=x0)
     sec = timed(lambda: (sim.reset(x0_ball=x0), sim.run(acts, n_steps=steps, hold=HOLD)), reps=reps)
     live = int(sim.stats().cpu().numpy()[_capi.ST_EVENTS0 + 10])
     out = {"players_per_team": n_team, "mode": mode, "games": n_games, "steps": steps, "ms": sec * 1e3,
            "live_game_steps": live, "game_steps_per_s": live / sec}
+    if noise:
+        out["noise"] = noise
     if peak_tflops:
         w = (W_REF if mode == "exact" else W_AFF)[n_team]
         out["roofline"] = {"bound": "fp64-issue" if mode != "fast" else "fp32-issue", "flop_per_game_step": w,
@@ -151,6 +154,7 @@ def measure_extras(device, hbm_peak_gbs):
                 rollout_rate(4, "exact", 100_000, 100, pk64.value), rollout_rate(7, "exact", 100_000, 100, pk64.value)],
         "collision_batch": rollout_rate(2, "exact", 100_000, 400, pk64.value, reps=3),
         "sampler_tick": sampler_tick(),
+        "noise": [rollout_rate(2, "fast", 200_000, 200, reps=3, noise=0.05), rollout_rate(2, "fast64", 100_000, 200, reps=3, noise=0.05)],
         "logging": logging_runs(hbm_peak_gbs),
     }
     out["configs"]["sampler_tick_ms"] = out["configs"]["sampler_tick"]["device_ms"]
