@@ -241,6 +241,26 @@ def test_resume_synth_stats_and_host_entry(rgs):
     assert dec.any() and np.allclose(g["t"][dec], 0.05 * ev[dec, tl.EV["DECIDED_STEP"]])
 
 
+@pytest.mark.parametrize("mode", ["fast", "exact"])
+def test_host_entry_chunked_equals_device_entry(rgs, mode):
+    """rgs_batch_run_host splits batches of >= 65 536 games into game-range chunks over two private streams (copies
+    overlapped with the rollouts); 70 001 games is ragged against every chunk bound.  Same bits as reset + run on
+    device tensors, statistics included; then once more on the same batch object (staging buffers reused)."""
+    n, steps, hold = 70_001, 40, 10
+    dx0, dacts = rgs.synth_inputs(n, steps // hold, seed=17)
+    sim = rgs.BatchedGameSim(n, mode=mode, winning_score=2)
+    dacts = dacts.to(sim.action_dtype)
+    sim.reset(x0_ball=dx0)
+    sim.run(dacts, n_steps=steps, hold=hold)
+    want = (sim.state().cpu().numpy(), sim.events().cpu().numpy(), sim.stats().cpu().numpy())
+    host = rgs.BatchedGameSim(n, mode=mode, winning_score=2)
+    hx0, hacts = dx0.cpu().pin_memory(), dacts.cpu().pin_memory()
+    for _ in range(2):
+        hs, he, hst = host.run_host(hx0, hacts, steps, hold=hold)
+        assert np.array_equal(hs, want[0]) and np.array_equal(he, want[1]) and np.array_equal(hst, want[2])
+    assert int(want[1][:, 2:8].sum()) > n // 10     # the games did collide
+
+
 # ------------------------------------------------------------------ K2: throughput formulation
 def test_fast64_tracks_oracle(rgs):
     """K2's formulation in fp64 against the UNMODIFIED oracle (absolute clock) over 200 steps.  Measured
